@@ -1,0 +1,172 @@
+/* sphb200.h — C ABI of the B200-native SPHinXsys particle-interaction path.
+ *
+ * Plain C: opaque handles, plain pointers and sizes, no C++/torch types.  One context per GPU
+ * (per rank).  Every entry point cites the reference interface it replaces; paths are relative to
+ * the reference tree's src/shared/ unless noted.  All calls are asynchronous on the context's
+ * stream except those that return a value to the host (…_dt with a non-NULL out pointer,
+ * var_to_host, reductions, debug dumps), which synchronise that stream.
+ *
+ * Error convention: the reference prints and exit(1)s (e.g. particle_iterators.h:51-53); this ABI
+ * returns a status and keeps a per-context message (sphb200_last_error).  It never exits.
+ *
+ * Ordering contract: sphb200_cell_list_update physically reorders the body's particles by linear
+ * cell index (the cell list IS the counting sort), permuting every registered variable and keeping
+ * OriginalID / SortedID consistent exactly as ParticleSorting does
+ * (particle_dynamics/configuration_dynamics/particle_sorting.cpp:16-23,55-58).
+ */
+#ifndef SPHB200_H
+#define SPHB200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sphb200_ctx sphb200_ctx;
+typedef struct sphb200_body sphb200_body;
+typedef struct sphb200_relation sphb200_relation;
+typedef int sphb200_status;
+
+enum
+{
+    SPHB200_OK = 0,
+    SPHB200_ERR_INVALID = 1,   /* bad argument / call order */
+    SPHB200_ERR_CUDA = 2,      /* CUDA runtime error (message holds cudaGetErrorString) */
+    SPHB200_ERR_NOT_FOUND = 3, /* variable not registered */
+    SPHB200_ERR_NO_DEVICE = 4  /* no CUDA device: there is NO CPU fallback */
+};
+
+/* ---- context ------------------------------------------------------------------------------- */
+/* Replaces SPHSystem (sphinxsys_system/sph_system.cpp:36-51) for the path: system bounds are the
+ * already expanded bounds (user box ± 4 dp).  ndim = 2|3 (SPH_NDIM), real_bytes = 8|4
+ * (SPHINXSYS_USE_FLOAT, common/base_data_type.h:50-60). */
+sphb200_status sphb200_ctx_create(int device, int ndim, int real_bytes, const double *sys_lo, const double *sys_hi,
+                                  sphb200_ctx **out);
+void sphb200_ctx_destroy(sphb200_ctx *ctx);
+sphb200_status sphb200_ctx_synchronize(sphb200_ctx *ctx);
+const char *sphb200_last_error(sphb200_ctx *ctx);
+/* the cudaStream_t all work of this context is enqueued on (for CUDA-event timing by the caller) */
+void *sphb200_ctx_stream(sphb200_ctx *ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+int64_t sphb200_ctx_launch_count(sphb200_ctx *ctx);
+
+/* ---- bodies and named variables ------------------------------------------------------------ */
+/* SPHBody/RealBody + SPHAdaptation (bodies/base_body.h:62-201, adaptations/adaptation.cpp:12-19):
+ * h = h_ratio*dp, Wendland C2 (kernels/kernel_wendland_c2.cpp:8-35), cell-linked-list mesh with
+ * spacing = cut-off radius and 2 buffer cells (meshes/cell_linked_list.cpp:10-20, base_mesh.cpp:6-16),
+ * sigma0 = lattice number density (adaptation.cpp:26-60). */
+sphb200_status sphb200_body_create(sphb200_ctx *ctx, const char *name, int64_t n, double dp, double h_ratio,
+                                   sphb200_body **out);
+/* WeaklyCompressibleFluid(rho0,c0) + Viscosity(mu) (materials/weakly_compressible_fluid.cpp:8-30) */
+sphb200_status sphb200_body_set_fluid(sphb200_body *b, double rho0, double c0, double mu);
+/* NeoHookeanSolid(rho0,E,nu) (materials/elastic_solid.cpp:54-80) */
+sphb200_status sphb200_body_set_elastic(sphb200_body *b, double rho0, double youngs, double poisson);
+/* PeriodicAlongAxis (particle_dynamics/general_dynamics/domian_bouding/domain_bounding.h:49-70) */
+sphb200_status sphb200_body_set_periodic(sphb200_body *b, int axis, double lo, double hi);
+/* out[0..11] = h, rc, W0, sigma0, mesh lo[3], mesh spacing, cells[3], n */
+sphb200_status sphb200_body_info(sphb200_body *b, double *out12);
+
+/* BaseParticles::registerStateVariable / addEvolvingVariable (particles/base_particles.h:119-162).
+ * width = Reals per particle (1 scalar, ndim Vecd, ndim*ndim Matd), array-of-Vecd layout
+ * (common/sphinxsys_variable.h:204-236).  host_ptr is BORROWED for the body's lifetime (may be NULL
+ * for a device-only variable, cf. DeviceOnlyDiscreteVariable, sphinxsys_variable.h:365-377).
+ * The device mirror is zero-initialised. Registering an existing name rebinds host_ptr. */
+sphb200_status sphb200_var_register(sphb200_body *b, const char *name, int width, int evolving, void *host_ptr);
+/* DiscreteVariable::synchronizeToDevice / synchronizeWithDevice (sphinxsys_variable.h:179-190;
+ * SYCL twin src_sycl/shared/common/sphinxsys_variable_sycl.hpp:35-87) */
+sphb200_status sphb200_var_to_device(sphb200_body *b, const char *name);
+sphb200_status sphb200_var_to_host(sphb200_body *b, const char *name);
+/* explicit-buffer variants (host buffer of n*width Reals) */
+sphb200_status sphb200_var_upload(sphb200_body *b, const char *name, const void *src);
+sphb200_status sphb200_var_download(sphb200_body *b, const char *name, void *dst);
+/* DelegatedData(par_device): raw device pointer, valid until the next cell_list_update of b */
+sphb200_status sphb200_var_device_ptr(sphb200_body *b, const char *name, void **out);
+/* OriginalID / SortedID (particles/base_particles.cpp:33-38), widened to int64 */
+sphb200_status sphb200_ids_to_host(sphb200_body *b, int64_t *original_id, int64_t *sorted_id);
+
+/* ---- spatial search ------------------------------------------------------------------------ */
+/* RealBody::updateCellLinkedList (bodies/base_body.cpp:113-116 → meshes/cell_linked_list.cpp:84-101;
+ * CK twin shared_ck/.../update_cell_linked_list.hpp:75-106) fused with ParticleSorting::exec
+ * (configuration_dynamics/particle_sorting.hpp:15-21): histogram → scan → scatter, then every
+ * variable is gathered into cell order.  Takes the position snapshot the pair geometry is frozen to. */
+sphb200_status sphb200_cell_list_update(sphb200_body *b);
+/* parity/debug: per particle (current order) linear cell index (base_mesh.hxx:68-78) and the
+ * reference's 10-bit Morton key (base_mesh.hxx:80-99) */
+sphb200_status sphb200_cell_keys(sphb200_body *b, int64_t *linear, int64_t *morton);
+/* parity/debug: CellOffset array (cells+1 entries) of the CSR cell list */
+sphb200_status sphb200_cell_offsets(sphb200_body *b, int64_t *out, int64_t *n_cells);
+/* PeriodicConditionUsingCellLinkedList::bounding_ (domain_bounding.h:93-137): wrap positions */
+sphb200_status sphb200_periodic_bounding(sphb200_body *b, int axis);
+
+/* InnerRelation / ContactRelation (body_relations/inner_body_relation.cpp:14-20,
+ * contact_body_relation.cpp:22-32) */
+sphb200_status sphb200_relation_inner_create(sphb200_body *b, sphb200_relation **out);
+sphb200_status sphb200_relation_contact_create(sphb200_body *b, sphb200_body *const *targets, int n_targets,
+                                               sphb200_relation **out);
+/* SPHRelation::updateConfiguration (base_body_relation.h:100; searchNeighborsByMesh
+ * meshes/cell_linked_list.hpp:20-46 with NeighborBuilderInner/Contact neighborhood.cpp:85-98,147-160).
+ * Builds a compact u32 neighbour-index list (count → scan → fill, cf. CK update_body_relation.hpp:117-164). */
+sphb200_status sphb200_relation_update(sphb200_relation *r);
+/* parity/debug: counts[n] and flat neighbour indices (list order) of target k; returns the total */
+sphb200_status sphb200_relation_neighbors(sphb200_relation *r, int k, int32_t *counts, int64_t *j_out, int64_t *total);
+
+/* ---- weakly compressible fluid dynamics ---------------------------------------------------- */
+/* DensitySummation<Inner<>|Inner<FreeSurface>> (+Contact<>) interaction+update
+ * (fluid_dynamics/density_summation.cpp:8-22,58-78; density_summation.hpp:11-32) */
+sphb200_status sphb200_density_summation(sphb200_relation *inner, sphb200_relation *contact_or_null, int free_surface);
+/* Integration1stHalf<Inner<>,Riemann|NoRiemann,NoKernelCorrection> (+Contact<Wall>) as Dynamics1Level:
+ * initialization + interaction + update (fluid_dynamics/fluid_integration.hpp:50-113).  Also
+ * accumulates max(c0+|v|) on the device so the following sphb200_acoustic_dt costs no extra pass. */
+sphb200_status sphb200_integration_1st_half(sphb200_relation *inner, sphb200_relation *wall_or_null, int riemann, double dt);
+/* Integration2ndHalf<Inner<>,Riemann|NoRiemann> (+Contact<Wall>) (fluid_integration.hpp:167-231) */
+sphb200_status sphb200_integration_2nd_half(sphb200_relation *inner, sphb200_relation *wall_or_null, int riemann, double dt);
+/* ReduceDynamics<AcousticTimeStep> (fluid_dynamics/fluid_time_step.cpp:12-31): cfl*h/(max(c0+|v|)+tiny) */
+sphb200_status sphb200_acoustic_dt(sphb200_body *b, double cfl, double *dt_out);
+/* ReduceDynamics<AdvectionTimeStep|AdvectionViscousTimeStep> (fluid_time_step.cpp:44-79) */
+sphb200_status sphb200_advection_dt(sphb200_body *b, double U_ref, double cfl, int viscous, double *dt_out);
+/* SimpleDynamics<GravityForce<Gravity>> (general_dynamics/force_prior.hpp:22-41) */
+sphb200_status sphb200_gravity_force(sphb200_body *b, const double *g);
+/* InteractionWithUpdate<ViscousForceInner> (fluid_dynamics/viscous_dynamics.hpp:35-53 + force_prior.hpp:22-26) */
+sphb200_status sphb200_viscous_force(sphb200_relation *inner);
+/* InteractionWithUpdate<TransportVelocityCorrectionInner<…TruncatedLinear,AllParticles>>
+ * (fluid_dynamics/transport_velocity_correction.hpp:38-67) */
+sphb200_status sphb200_transport_velocity_correction(sphb200_relation *inner, double coefficient);
+/* ReducedQuantityRecording observables (general_dynamics/general_reduce.cpp:18-79) */
+sphb200_status sphb200_total_kinetic_energy(sphb200_body *b, double *out);
+sphb200_status sphb200_total_mechanical_energy(sphb200_body *b, const double *g, double *out);
+sphb200_status sphb200_maximum_speed(sphb200_body *b, double *out);
+/* ObservingAQuantity (general_dynamics/general_interpolation.h:63-83): out = n_observer*width doubles */
+sphb200_status sphb200_observe(sphb200_relation *contact, const char *name, int width, double *out);
+
+/* ---- total-Lagrangian elastic solid -------------------------------------------------------- */
+/* LinearGradientCorrectionMatrix<Inner<>> (general_dynamics/kernel_correction.cpp:8-29) */
+sphb200_status sphb200_correction_matrix(sphb200_relation *inner);
+/* Dynamics1Level<DecomposedIntegration1stHalf | Integration1stHalfPK2>
+ * (solid_dynamics/elastic_dynamics.h:171-207,259-287; elastic_dynamics.cpp:96-118,162-184) */
+sphb200_status sphb200_solid_1st_half(sphb200_relation *inner, int decomposed, double dt);
+/* Dynamics1Level<solid_dynamics::Integration2ndHalf> (elastic_dynamics.h:325-351, .cpp:186-194) */
+sphb200_status sphb200_solid_2nd_half(sphb200_relation *inner, double dt);
+/* SimpleDynamics<FixBodyPartConstraint> over ORIGINAL particle ids (general_constraint.h:106-121) */
+sphb200_status sphb200_solid_constrain(sphb200_body *b, const int64_t *original_ids, int64_t n);
+/* ReduceDynamics<solid_dynamics::AcousticTimeStep> (elastic_dynamics.cpp:12-30), ReduceMin */
+sphb200_status sphb200_solid_dt(sphb200_body *b, double cfl, double *dt_out);
+
+/* ---- primitives exposed for the reference's own known-answer tests -------------------------- */
+/* exclusive_scan(policy, first, d_first, n, plus) (common/algorithm_primitive.h:209-279; SYCL twin
+ * src_sycl/shared/common/algorithm_primitive_sycl.h:96-122).  Host in/out buffers of n uint32;
+ * returns the total like the reference's overload. */
+sphb200_status sphb200_exclusive_scan_u32(sphb200_ctx *ctx, const uint32_t *in, uint32_t *out, int64_t n, uint64_t *total);
+
+/* ---- slab decomposition helpers (multi-GPU; no reference equivalent) ------------ */
+/* gather rows `idx[0..m)` (current order) of variable `name` into a packed device buffer / scatter back */
+sphb200_status sphb200_var_gather(sphb200_body *b, const char *name, const int64_t *idx_dev, int64_t m, void *dst_dev);
+sphb200_status sphb200_var_scatter(sphb200_body *b, const char *name, const int64_t *idx_dev, int64_t m, const void *src_dev);
+/* change the number of particles (migration in/out); keeps the first min(n_old,n_new) rows */
+sphb200_status sphb200_body_resize(sphb200_body *b, int64_t n_new);
+/* particles [n_owned, n) are ghosts: they take part as neighbours j but are skipped as i by the
+ * dynamics and reductions (their state is refreshed by the halo exchange) */
+sphb200_status sphb200_body_set_owned(sphb200_body *b, int64_t n_owned);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPHB200_H */

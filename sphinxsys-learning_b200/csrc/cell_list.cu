@@ -1,0 +1,492 @@
+// Cell-linked-list construction fused with the cell-index particle sort.
+//
+// Reference behaviour reproduced:
+//   meshes/base_mesh.hxx:9-26,68-99          cell index / linear index / Morton key
+//   meshes/cell_linked_list.cpp:84-101        UpdateCellLists (index lists + position copies)
+//   shared_ck/.../update_cell_linked_list.hpp:40-106   count → scan → scatter (CSR CellOffset)
+//   configuration_dynamics/particle_sorting.cpp:16-58  sort of all evolving variables + ID maps
+//
+// B200 design: the cell list IS a counting sort.  One pass computes the linear cell of every particle
+// and its rank inside the cell with warp-aggregated atomics (__match_any_sync groups the lanes that
+// fall in the same cell, one atomicAdd per group); a scan gives CellOffset; a scatter gives the
+// permutation, made deterministic (stable) by ordering each cell's few entries by their previous
+// index; every registered variable is then gathered into cell order, so afterwards the particles of a
+// cell - and of a run of cells along the fastest axis - are contiguous in HBM and neighbour gathers
+// hit consecutive sectors.  The frozen position snapshot + Vol is packed into one aligned Real4 record
+// per particle (xV) so a neighbour costs one 16/32-byte load.
+#include "internal.cuh"
+
+using namespace sphb;
+
+namespace sphb
+{
+// ---------------------------------------------------------------------------------------------
+// exclusive scan (u32): 3-phase, 4096 items per block
+// ---------------------------------------------------------------------------------------------
+constexpr int kScanBlock = 1024;
+constexpr int kScanItems = 4;
+constexpr int kScanTile = kScanBlock * kScanItems;
+
+__device__ __forceinline__ u32 blockExclusiveScan(u32 v, u32 *warp_sums, u32 &block_total)
+{
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    u32 inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+        u32 t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o)
+            inc += t;
+    }
+    if (lane == 31)
+        warp_sums[wid] = inc;
+    __syncthreads();
+    if (wid == 0)
+    {
+        u32 w = lane < (blockDim.x >> 5) ? warp_sums[lane] : 0;
+        u32 winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            u32 t = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o)
+                winc += t;
+        }
+        warp_sums[lane] = winc - w;
+        if (lane == 31)
+            warp_sums[32] = winc;
+    }
+    __syncthreads();
+    block_total = warp_sums[32];
+    u32 r = warp_sums[wid] + inc - v;
+    __syncthreads();
+    return r;
+}
+
+__global__ void __launch_bounds__(kScanBlock) k_scan_tiles(const u32 *in, u32 *out, u32 *tile_sums, int64_t n)
+{
+    __shared__ u32 ws[33];
+    int64_t base = int64_t(blockIdx.x) * kScanTile + int64_t(threadIdx.x) * kScanItems;
+    u32 v[kScanItems];
+    u32 s = 0;
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k)
+    {
+        v[k] = (base + k < n) ? in[base + k] : 0;
+        s += v[k];
+    }
+    u32 total;
+    u32 ex = blockExclusiveScan(s, ws, total);
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k)
+    {
+        if (base + k < n)
+            out[base + k] = ex;
+        ex += v[k];
+    }
+    if (threadIdx.x == 0)
+        tile_sums[blockIdx.x] = total;
+}
+// single block: exclusive scan of the tile sums in place; total → tile_sums[n_tiles]
+__global__ void __launch_bounds__(kScanBlock) k_scan_tile_sums(u32 *tile_sums, int64_t n_tiles)
+{
+    __shared__ u32 ws[33];
+    u32 carry = 0;
+    for (int64_t base = 0; base < n_tiles; base += kScanBlock)
+    {
+        int64_t i = base + threadIdx.x;
+        u32 v = i < n_tiles ? tile_sums[i] : 0;
+        u32 total;
+        u32 ex = blockExclusiveScan(v, ws, total);
+        if (i < n_tiles)
+            tile_sums[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0)
+        tile_sums[n_tiles] = carry;
+}
+__global__ void k_scan_add(u32 *out, const u32 *tile_sums, int64_t n, int64_t n_tiles, int with_total)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i < n)
+        out[i] += tile_sums[i / kScanTile];
+    if (with_total && i == 0)
+        out[n] = tile_sums[n_tiles];
+}
+
+sphb200_status exclusiveScanU32(sphb200_ctx *ctx, const u32 *in, u32 *out, int64_t n, bool with_total)
+{
+    if (n <= 0)
+    {
+        if (with_total)
+            SPHB_CUDA(ctx, cudaMemsetAsync(out, 0, 4, ctx->stream));
+        return SPHB200_OK;
+    }
+    int64_t n_tiles = (n + kScanTile - 1) / kScanTile;
+    SPHB_CUDA(ctx, ctx->scan_tmp.ensure(size_t(n_tiles + 1) * 4));
+    u32 *ts = static_cast<u32 *>(ctx->scan_tmp.p);
+    k_scan_tiles<<<int(n_tiles), kScanBlock, 0, ctx->stream>>>(in, out, ts, n);
+    SPHB_LAUNCH_CHECK(ctx);
+    k_scan_tile_sums<<<1, kScanBlock, 0, ctx->stream>>>(ts, n_tiles);
+    SPHB_LAUNCH_CHECK(ctx);
+    k_scan_add<<<gridFor(n, 256), 256, 0, ctx->stream>>>(out, ts, n, n_tiles, with_total ? 1 : 0);
+    SPHB_LAUNCH_CHECK(ctx);
+    return SPHB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// binning
+// ---------------------------------------------------------------------------------------------
+template <int D, class R>
+__global__ void __launch_bounds__(256) k_bin(const R *__restrict__ pos, int64_t n, MeshP<D, R> mesh,
+                                             u32 *__restrict__ cell_of, u32 *__restrict__ rank,
+                                             u32 *__restrict__ cell_count)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    bool active = i < n;
+    u32 c = 0xffffffffu;
+    if (active)
+    {
+        R x[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d)
+            x[d] = pos[i * D + d];
+        int ci[D];
+        mesh.cellIndex(x, ci);
+        c = mesh.linear(ci);
+    }
+    // warp-aggregated atomic: lanes with the same cell elect a leader that adds the group size
+    unsigned amask = __ballot_sync(0xffffffffu, active);
+    if (active)
+    {
+        unsigned peers = __match_any_sync(amask, c);
+        int leader = __ffs(peers) - 1;
+        int lane = threadIdx.x & 31;
+        u32 base = 0;
+        if (lane == leader)
+            base = atomicAdd(cell_count + c, u32(__popc(peers)));
+        base = __shfl_sync(peers, base, leader);
+        cell_of[i] = c;
+        rank[i] = base + u32(__popc(peers & ((1u << lane) - 1u)));
+    }
+}
+
+__global__ void __launch_bounds__(256) k_scatter_perm(const u32 *__restrict__ cell_of, const u32 *__restrict__ rank,
+                                                      const u32 *__restrict__ cell_offset, u32 *__restrict__ perm,
+                                                      int64_t n)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i < n)
+        perm[cell_offset[cell_of[i]] + rank[i]] = u32(i);
+}
+
+// order the entries of every cell by previous particle index: makes the sort stable and the whole
+// configuration (hence every floating-point sum order) reproducible run to run
+__global__ void __launch_bounds__(256) k_cell_order(const u32 *__restrict__ cell_offset, u32 *__restrict__ perm,
+                                                    int64_t n_cells)
+{
+    int64_t c = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (c >= n_cells)
+        return;
+    u32 b = cell_offset[c], e = cell_offset[c + 1];
+    for (u32 k = b + 1; k < e; ++k)
+    {
+        u32 v = perm[k];
+        u32 m = k;
+        while (m > b && perm[m - 1] > v)
+        {
+            perm[m] = perm[m - 1];
+            --m;
+        }
+        perm[m] = v;
+    }
+}
+
+// gather of one variable into the new order; T = element type, width elements per particle
+template <class T>
+__global__ void __launch_bounds__(256) k_permute(const T *__restrict__ src, T *__restrict__ dst,
+                                                 const u32 *__restrict__ perm, int64_t n, int width)
+{
+    int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (t >= n * width)
+        return;
+    int64_t i = t / width;
+    int d = int(t - i * width);
+    dst[t] = src[int64_t(perm[i]) * width + d];
+}
+
+__global__ void __launch_bounds__(256) k_permute_ids(const u32 *__restrict__ oid_src, u32 *__restrict__ oid_dst,
+                                                     u32 *__restrict__ sorted_id, const u32 *__restrict__ cell_src,
+                                                     u32 *__restrict__ cell_dst, const u32 *__restrict__ perm, int64_t n)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    u32 p = perm[i];
+    u32 o = oid_src[p];
+    oid_dst[i] = o;
+    sorted_id[o] = u32(i); // particle_sorting.cpp:55-58 UpdateSortedID
+    cell_dst[i] = cell_src[p];
+}
+
+template <int D, class R>
+__global__ void __launch_bounds__(256) k_pack_xV(const R *__restrict__ pos, const R *__restrict__ vol,
+                                                 typename Real4<R>::type *__restrict__ xV, int64_t n, int vol_only)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    typename Real4<R>::type v;
+    if (vol_only)
+    {
+        v = xV[i];
+    }
+    else
+    {
+        v.x = pos[i * D];
+        v.y = pos[i * D + 1];
+        v.z = D == 3 ? pos[i * D + (D - 1)] : R(0);
+    }
+    v.w = vol[i];
+    xV[i] = v;
+}
+
+template <int D, class R>
+__global__ void __launch_bounds__(256) k_periodic_bounding(R *__restrict__ pos, int64_t n, int axis, R lo, R hi)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    // domain_bounding.h:101-137: checkLowerBound then checkUpperBound
+    R L = hi - lo;
+    R x = pos[i * D + axis];
+    if (x < lo)
+        x += L;
+    if (x > hi)
+        x -= L;
+    pos[i * D + axis] = x;
+}
+
+__host__ __device__ inline u64 mortonPart(u64 i)
+{
+    // base_mesh.hxx:80-90: 10-bit spread
+    u64 x = i;
+    x &= 0x3ff;
+    x = (x | x << 16) & 0x30000ff;
+    x = (x | x << 8) & 0x300f00f;
+    x = (x | x << 4) & 0x30c30c3;
+    x = (x | x << 2) & 0x9249249;
+    return x;
+}
+
+template <int D, class R>
+__global__ void __launch_bounds__(256) k_cell_keys(const R *__restrict__ pos, int64_t n, MeshP<D, R> mesh,
+                                                   long long *__restrict__ linear, long long *__restrict__ morton)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    R x[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d)
+        x[d] = pos[i * D + d];
+    int c[D];
+    mesh.cellIndex(x, c);
+    linear[i] = (long long)mesh.linear(c);
+    u64 m = mortonPart(u64(c[0])) | (mortonPart(u64(c[1])) << 1);
+    if (D == 3)
+        m |= mortonPart(u64(c[D - 1])) << 2;
+    morton[i] = (long long)m;
+}
+
+template <int D, class R>
+sphb200_status ensurePacked(sphb200_body *b)
+{
+    sphb200_ctx *ctx = b->ctx;
+    if (!b->cell_list_valid)
+        return ctx->fail(SPHB200_ERR_INVALID, "body '" + b->name + "': cell_list_update has not been called");
+    if (!b->xV_vol_dirty || b->n == 0)
+        return SPHB200_OK;
+    R *pos, *vol;
+    SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos));
+    SPHB_TRY(getVarPtr<R>(b, "VolumetricMeasure", 1, &vol));
+    k_pack_xV<D, R><<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(
+        pos, vol, static_cast<typename Real4<R>::type *>(b->xV.p), b->n, 1);
+    SPHB_LAUNCH_CHECK(ctx);
+    b->xV_vol_dirty = false;
+    return SPHB200_OK;
+}
+template sphb200_status ensurePacked<2, float>(sphb200_body *);
+template sphb200_status ensurePacked<2, double>(sphb200_body *);
+template sphb200_status ensurePacked<3, float>(sphb200_body *);
+template sphb200_status ensurePacked<3, double>(sphb200_body *);
+
+template <int D, class R>
+static sphb200_status cellListUpdate(sphb200_body *b)
+{
+    sphb200_ctx *ctx = b->ctx;
+    cudaStream_t st = ctx->stream;
+    const int64_t n = b->n;
+    BodyP<D, R> &P = b->P<D, R>();
+    const int64_t nc = b->n_cells;
+    const size_t nb = size_t(n > 0 ? n : 1);
+    SPHB_CUDA(ctx, b->cell_of.ensure(nb * 4));
+    SPHB_CUDA(ctx, b->rank_in_cell.ensure(nb * 4));
+    SPHB_CUDA(ctx, b->perm.ensure(nb * 4));
+    SPHB_CUDA(ctx, b->cell_count.ensure(size_t(nc + 1) * 4));
+    SPHB_CUDA(ctx, b->cell_offset.ensure(size_t(nc + 1) * 4));
+    SPHB_CUDA(ctx, b->xV.ensure(nb * 4 * sizeof(R)));
+    SPHB_CUDA(ctx, ctx->scratch_a.ensure(nb * 4));
+    SPHB_CUDA(ctx, ctx->scratch_b.ensure(nb * 4));
+    u32 *cell_of = static_cast<u32 *>(b->cell_of.p), *rank = static_cast<u32 *>(b->rank_in_cell.p),
+        *perm = static_cast<u32 *>(b->perm.p), *cnt = static_cast<u32 *>(b->cell_count.p),
+        *off = static_cast<u32 *>(b->cell_offset.p);
+    R *pos, *vol;
+    SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos));
+    SPHB_CUDA(ctx, cudaMemsetAsync(cnt, 0, size_t(nc + 1) * 4, st));
+    if (n > 0)
+    {
+        k_bin<D, R><<<gridFor(n, 256), 256, 0, st>>>(pos, n, P.mesh, cell_of, rank, cnt);
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    SPHB_TRY(exclusiveScanU32(ctx, cnt, off, nc, true));
+    if (n > 0)
+    {
+        k_scatter_perm<<<gridFor(n, 256), 256, 0, st>>>(cell_of, rank, off, perm, n);
+        SPHB_LAUNCH_CHECK(ctx);
+        k_cell_order<<<gridFor(nc, 256), 256, 0, st>>>(off, perm, nc);
+        SPHB_LAUNCH_CHECK(ctx);
+        // gather every registered variable into cell order (UpdateSortableVariables,
+        // shared_ck/.../base_configuration_dynamics.h:74-128, one temp buffer swapped in)
+        for (auto &kv : b->vars)
+        {
+            Var &v = *kv.second;
+            SPHB_CUDA(ctx, b->tmp_var.ensure(v.dev.bytes));
+            k_permute<R><<<gridFor(n * v.width, 256), 256, 0, st>>>(static_cast<const R *>(v.dev.p),
+                                                                    static_cast<R *>(b->tmp_var.p), perm, n, v.width);
+            SPHB_LAUNCH_CHECK(ctx);
+            std::swap(v.dev, b->tmp_var);
+        }
+        u32 *oid_tmp = static_cast<u32 *>(ctx->scratch_a.p), *cell_tmp = static_cast<u32 *>(ctx->scratch_b.p);
+        k_permute_ids<<<gridFor(n, 256), 256, 0, st>>>(static_cast<const u32 *>(b->original_id.p), oid_tmp,
+                                                      static_cast<u32 *>(b->sorted_id.p), cell_of, cell_tmp, perm, n);
+        SPHB_LAUNCH_CHECK(ctx);
+        SPHB_CUDA(ctx, cudaMemcpyAsync(b->original_id.p, oid_tmp, size_t(n) * 4, cudaMemcpyDeviceToDevice, st));
+        SPHB_CUDA(ctx, cudaMemcpyAsync(cell_of, cell_tmp, size_t(n) * 4, cudaMemcpyDeviceToDevice, st));
+        SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos));
+        SPHB_TRY(getVarPtr<R>(b, "VolumetricMeasure", 1, &vol));
+        k_pack_xV<D, R><<<gridFor(n, 256), 256, 0, st>>>(pos, vol, static_cast<typename Real4<R>::type *>(b->xV.p), n, 0);
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    b->cell_list_valid = true;
+    b->xV_vol_dirty = false;
+    b->config_stamp++;
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status cellKeys(sphb200_body *b, int64_t *linear, int64_t *morton)
+{
+    sphb200_ctx *ctx = b->ctx;
+    const int64_t n = b->n;
+    if (n == 0)
+        return SPHB200_OK;
+    SPHB_CUDA(ctx, ctx->scratch_a.ensure(size_t(n) * 8));
+    SPHB_CUDA(ctx, ctx->scratch_b.ensure(size_t(n) * 8));
+    R *pos;
+    SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos));
+    k_cell_keys<D, R><<<gridFor(n, 256), 256, 0, ctx->stream>>>(pos, n, b->P<D, R>().mesh,
+                                                              static_cast<long long *>(ctx->scratch_a.p),
+                                                              static_cast<long long *>(ctx->scratch_b.p));
+    SPHB_LAUNCH_CHECK(ctx);
+    if (linear)
+        SPHB_CUDA(ctx, cudaMemcpyAsync(linear, ctx->scratch_a.p, size_t(n) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (morton)
+        SPHB_CUDA(ctx, cudaMemcpyAsync(morton, ctx->scratch_b.p, size_t(n) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status periodicBounding(sphb200_body *b, int axis)
+{
+    sphb200_ctx *ctx = b->ctx;
+    if (b->n == 0)
+        return SPHB200_OK;
+    R *pos;
+    SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos));
+    BodyP<D, R> &P = b->P<D, R>();
+    k_periodic_bounding<D, R><<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(pos, b->n, axis, P.per.lo[axis], P.per.hi[axis]);
+    SPHB_LAUNCH_CHECK(ctx);
+    return SPHB200_OK;
+}
+} // namespace sphb
+
+extern "C"
+{
+sphb200_status sphb200_cell_list_update(sphb200_body *b)
+{
+    if (!b)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, cellListUpdate, b);
+}
+
+sphb200_status sphb200_cell_keys(sphb200_body *b, int64_t *linear, int64_t *morton)
+{
+    if (!b)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, cellKeys, b, linear, morton);
+}
+
+sphb200_status sphb200_cell_offsets(sphb200_body *b, int64_t *out, int64_t *n_cells)
+{
+    if (!b)
+        return SPHB200_ERR_INVALID;
+    sphb200_ctx *ctx = b->ctx;
+    if (n_cells)
+        *n_cells = b->n_cells;
+    if (!out)
+        return SPHB200_OK;
+    if (!b->cell_list_valid)
+        return ctx->fail(SPHB200_ERR_INVALID, "cell_offsets: cell_list_update has not been called");
+    cudaSetDevice(ctx->device);
+    std::vector<u32> tmp;
+    tmp.resize(size_t(b->n_cells + 1));
+    SPHB_CUDA(ctx, cudaMemcpyAsync(tmp.data(), b->cell_offset.p, tmp.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (size_t i = 0; i < tmp.size(); ++i)
+        out[i] = int64_t(tmp[i]);
+    return SPHB200_OK;
+}
+
+sphb200_status sphb200_periodic_bounding(sphb200_body *b, int axis)
+{
+    if (!b || axis < 0 || axis >= b->ctx->ndim || !b->periodic[axis])
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, periodicBounding, b, axis);
+}
+
+sphb200_status sphb200_exclusive_scan_u32(sphb200_ctx *ctx, const uint32_t *in, uint32_t *out, int64_t n, uint64_t *total)
+{
+    if (!ctx || n < 0 || (n > 0 && (!in || !out)))
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    SPHB_CUDA(ctx, ctx->scratch_a.ensure(size_t(n + 1) * 4));
+    SPHB_CUDA(ctx, ctx->scratch_b.ensure(size_t(n + 1) * 4));
+    if (n > 0)
+        SPHB_CUDA(ctx, cudaMemcpyAsync(ctx->scratch_a.p, in, size_t(n) * 4, cudaMemcpyHostToDevice, ctx->stream));
+    SPHB_TRY(exclusiveScanU32(ctx, static_cast<u32 *>(ctx->scratch_a.p), static_cast<u32 *>(ctx->scratch_b.p), n, true));
+    std::vector<u32> tmp;
+    tmp.resize(size_t(n + 1));
+    SPHB_CUDA(ctx, cudaMemcpyAsync(tmp.data(), ctx->scratch_b.p, size_t(n + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (n > 0)
+        memcpy(out, tmp.data(), size_t(n) * 4);
+    if (total)
+        *total = tmp[size_t(n)];
+    return SPHB200_OK;
+}
+} // extern "C"

@@ -1,0 +1,1103 @@
+// Weakly-compressible fluid dynamics of the classic SPHinXsys path as fused sm_100a kernels.
+//
+// Reference local dynamics reproduced, one kernel per Dynamics algorithm instead
+// of one particle_for per initialization/interaction/update stage:
+//   fluid_dynamics/density_summation.cpp:8-22,58-78, density_summation.hpp:11-32
+//   fluid_dynamics/fluid_integration.hpp:50-113 (1st half), :167-231 (2nd half)
+//   fluid_dynamics/base_fluid_dynamics.h:54-75 (InteractionWithWall data)
+//   materials/riemann_solver.h:55-123, common/common_functors.h:82-94 (acoustic Riemann solver, limiter 3)
+//   materials/weakly_compressible_fluid.cpp:8-30 (EOS)
+//   fluid_dynamics/fluid_time_step.cpp:12-79 (time-step reductions, ReduceMax)
+//   fluid_dynamics/viscous_dynamics.hpp:35-53, general_dynamics/force_prior.hpp:10-41
+//   fluid_dynamics/transport_velocity_correction.hpp:38-67
+//   general_dynamics/general_reduce.cpp:18-79, general_interpolation.h:63-83
+//
+// Data flow per particle i (thread i): the SELL-32 index list is read coalesced (lane = i mod 32),
+// each neighbour costs one aligned Real4 gather of the frozen (x, Vol) record plus the gathered field
+// (p_j or v_j); W/dW/e/r are recomputed in registers.  Gather-only writes (index i only), exactly the
+// reference's write discipline, so no atomics on particle data.
+#include "internal.cuh"
+
+using namespace sphb;
+
+namespace sphb
+{
+template <class R>
+struct ListP
+{
+    const u32 *count, *slice_off, *list;
+};
+
+template <class R>
+struct FluidP
+{
+    R rho0, c0, p0, mu, h;
+    // riemann_solver.h:55-92 constants for identical left/right fluids
+    R inv_rho0c0_ave, rho0c0_geo_ave, inv_c0_ave, limiter_slope;
+    int riemann;
+};
+
+template <class R>
+static FluidP<R> makeFluidP(const sphb200_body *b, R h, bool riemann)
+{
+    FluidP<R> f;
+    f.rho0 = R(b->rho0);
+    f.c0 = R(b->c0);
+    f.p0 = f.rho0 * f.c0 * f.c0;
+    f.mu = R(b->mu);
+    f.h = h;
+    R a = f.rho0 * f.c0, c = f.rho0 * f.c0;
+    R inv_sum = R(1.0) / (a + c);
+    f.inv_rho0c0_ave = (a + c) / (std::pow(a, R(2)) + std::pow(c, R(2)));
+    f.rho0c0_geo_ave = R(2.0) * a * c * inv_sum;
+    f.inv_c0_ave = R(0.5) * (f.rho0 + f.rho0) * f.inv_rho0c0_ave;
+    f.limiter_slope = R(3.0);
+    f.riemann = riemann ? 1 : 0;
+    return f;
+}
+
+template <class R>
+__device__ __forceinline__ R dissipativePJump(const FluidP<R> &f, R u)
+{
+    // riemann_solver.h:109-114 with TruncatedLinear (common_functors.h:82-94)
+    R lim = fmin(f.limiter_slope * (f.inv_c0_ave * fmax(u, R(0))), R(1));
+    return f.riemann ? f.rho0c0_geo_ave * u * lim : R(0);
+}
+template <class R>
+__device__ __forceinline__ R dissipativeUJump(const FluidP<R> &f, R dp)
+{
+    return f.riemann ? dp * f.inv_rho0c0_ave : R(0);
+}
+
+template <int D, class R>
+__device__ __forceinline__ void loadVec(const R *__restrict__ a, u32 j, R *v)
+{
+#pragma unroll
+    for (int d = 0; d < D; ++d)
+        v[d] = __ldg(a + size_t(j) * D + d);
+}
+
+template <int D, class R>
+__device__ __forceinline__ void loadXj(const typename Real4<R>::type *__restrict__ xV, u32 j, R *x, R &w)
+{
+    typename Real4<R>::type v = ldg4(xV + j);
+    x[0] = v.x;
+    x[1] = v.y;
+    if (D == 3)
+        x[D - 1] = v.z;
+    w = v.w;
+}
+
+// ---------------------------------------------------------------------------------------------
+// DensitySummation
+// ---------------------------------------------------------------------------------------------
+template <int D, class R>
+__global__ void __launch_bounds__(128)
+    k_density_summation(int64_t n, const typename Real4<R>::type *xV, ListP<R> in, ContactP<R> ct,
+                        KernelP<R> kern, KernelP<R> kern_ct, PeriodicP<D, R> per, R rho0, R inv_sigma0,
+                        const R *__restrict__ mass, R *__restrict__ rho_sum, R *__restrict__ rho, R *__restrict__ vol,
+                        typename Real4<R>::type *xV_w, int free_surface)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    const int lane = threadIdx.x & 31;
+    R xi[D], Vi;
+    loadXj<D, R>(xV, u32(i), xi, Vi);
+    R sigma = kern.factor_W; // W0
+    {
+        const u32 cnt = in.count[i];
+        const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
+#pragma unroll 4
+        for (u32 k = 0; k < cnt; ++k)
+        {
+            u32 j = __ldg(lst + size_t(k) * 32u);
+            R xj[D], Vj;
+            loadXj<D, R>(xV, j, xj, Vj);
+            periodicImage<D, R>(xi, xj, per);
+            R r2 = R(0);
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+            {
+                R d = xi[a] - xj[a];
+                r2 += d * d;
+            }
+            sigma += kernelW<R>(sqrt_r(r2), kern);
+        }
+    }
+    R rs = sigma * rho0 * inv_sigma0;
+    if (ct.n > 0)
+    {
+        R s = R(0);
+        for (int t = 0; t < ct.n; ++t)
+        {
+            const TargetP<R> &T = ct.t[t];
+            const u32 cnt = T.count[i];
+            const u32 *lst = T.list + u64(T.slice_off[i >> 5]) * 32u + lane;
+            for (u32 k = 0; k < cnt; ++k)
+            {
+                u32 j = __ldg(lst + size_t(k) * 32u);
+                R xj[D], Vj;
+                loadXj<D, R>(T.xV, j, xj, Vj);
+                R r2 = R(0);
+#pragma unroll
+                for (int a = 0; a < D; ++a)
+                {
+                    R d = xi[a] - xj[a];
+                    r2 += d * d;
+                }
+                s += kernelW<R>(sqrt_r(r2), kern_ct) * T.inv_rho0 * __ldg(T.mass + j);
+            }
+        }
+        rs += s * rho0 * rho0 * inv_sigma0 / mass[i];
+    }
+    rho_sum[i] = rs;
+    if (free_surface)
+    {
+        rho[i] = fmax(rs, rho0); // density_summation.hpp:28-32
+    }
+    else
+    {
+        rho[i] = rs; // density_summation.cpp:18-22
+        R v = mass[i] / rs;
+        vol[i] = v;
+        // keep the packed Vol in step; no thread reads another particle's .w in this kernel
+        reinterpret_cast<R *>(xV_w + i)[3] = v;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Integration1stHalf: K1 initialization, K2 interaction (+wall) + update + max(c0+|v|)
+// ---------------------------------------------------------------------------------------------
+template <int D, class R>
+__global__ void __launch_bounds__(256)
+    k_first_half_init(int64_t n, R dt, R p0, R rho0, R *__restrict__ rho, const R *__restrict__ drho,
+                      R *__restrict__ p, R *__restrict__ pos, const R *__restrict__ vel)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    R r = rho[i] + drho[i] * dt * R(0.5);
+    rho[i] = r;
+    p[i] = p0 * (r / rho0 - R(1.0));
+#pragma unroll
+    for (int d = 0; d < D; ++d)
+        pos[i * D + d] += vel[i * D + d] * dt * R(0.5);
+}
+
+template <int D, class R>
+__global__ void __launch_bounds__(128)
+    k_first_half(int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, ContactP<R> wall,
+                 KernelP<R> kern, KernelP<R> kern_w, PeriodicP<D, R> per, FluidP<R> fl, R dt,
+                 const R *__restrict__ p, const R *__restrict__ rho, const R *__restrict__ mass,
+                 const R *__restrict__ fprior, R *__restrict__ force, R *__restrict__ drho, R *__restrict__ vel,
+                 unsigned long long *__restrict__ max_slot)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    R signal = R(0);
+    if (i < n)
+    {
+        R xi[D], Vi;
+        loadXj<D, R>(xV, u32(i), xi, Vi);
+        const R pi = p[i], rhoi = rho[i], mi = mass[i];
+        R f[D];
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            f[a] = R(0);
+        R diss = R(0);
+        {
+            const u32 cnt = in.count[i];
+            const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
+#pragma unroll 4
+            for (u32 k = 0; k < cnt; ++k)
+            {
+                u32 j = __ldg(lst + size_t(k) * 32u);
+                R xj[D], Vj;
+                loadXj<D, R>(xV, j, xj, Vj);
+                R pj = __ldg(p + j);
+                periodicImage<D, R>(xi, xj, per);
+                Pair<D, R> g;
+                pairGeometry<D, R>(xi, xj, kern, g);
+                R dWV = g.dW * Vj;
+                R ps = (pi + pj) * dWV;
+#pragma unroll
+                for (int a = 0; a < D; ++a)
+                    f[a] -= ps * g.e[a];
+                diss += dissipativeUJump<R>(fl, pi - pj) * dWV;
+            }
+        }
+        R fo[D], fp[D];
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+        {
+            fp[a] = fprior[i * D + a];
+            fo[a] = force[i * D + a] + f[a] * Vi;
+        }
+        R dr = diss * rhoi;
+        if (wall.n > 0)
+        {
+            R fw[D];
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+                fw[a] = R(0);
+            R dw = R(0);
+            R acc_i[D];
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+                acc_i[a] = fp[a] / mi;
+            for (int t = 0; t < wall.n; ++t)
+            {
+                const TargetP<R> &T = wall.t[t];
+                const u32 cnt = T.count[i];
+                const u32 *lst = T.list + u64(T.slice_off[i >> 5]) * 32u + lane;
+                for (u32 k = 0; k < cnt; ++k)
+                {
+                    u32 j = __ldg(lst + size_t(k) * 32u);
+                    R xj[D], Vj;
+                    loadXj<D, R>(T.xV, j, xj, Vj);
+                    R aw[D];
+                    loadVec<D, R>(T.acc, j, aw);
+                    Pair<D, R> g;
+                    pairGeometry<D, R>(xi, xj, kern_w, g);
+                    R dWV = g.dW * Vj;
+                    R face = R(0);
+#pragma unroll
+                    for (int a = 0; a < D; ++a)
+                        face += (acc_i[a] - aw[a]) * (-g.e[a]);
+                    R p_wall = pi + rhoi * g.r * fmax(R(0), face);
+                    R ps = (pi + p_wall) * dWV;
+#pragma unroll
+                    for (int a = 0; a < D; ++a)
+                        fw[a] -= ps * g.e[a];
+                    dw += dissipativeUJump<R>(fl, pi - p_wall) * dWV;
+                }
+            }
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+                fo[a] += fw[a] * Vi;
+            dr += dw * rhoi;
+        }
+        drho[i] = dr;
+        R v[D];
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+        {
+            force[i * D + a] = fo[a];
+            v[a] = vel[i * D + a] + (fp[a] + fo[a]) / mi * dt; // fluid_integration.hpp:58-61
+            vel[i * D + a] = v[a];
+        }
+        signal = fl.c0 + sqrt_r(sqnormExact<D, R>(v)); // fluid_time_step.cpp:21-24
+    }
+    signal = warpMax<R>(signal);
+    if (lane == 0)
+        atomicMaxNonNeg(max_slot, double(signal));
+}
+
+// ---------------------------------------------------------------------------------------------
+// Integration2ndHalf: initialization + interaction (+wall) + update in one kernel
+// ---------------------------------------------------------------------------------------------
+template <int D, class R>
+__global__ void __launch_bounds__(128)
+    k_second_half(int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, ContactP<R> wall,
+                  KernelP<R> kern, KernelP<R> kern_w, PeriodicP<D, R> per, FluidP<R> fl, R dt,
+                  const R *__restrict__ vel, R *__restrict__ pos, R *__restrict__ rho, R *__restrict__ drho,
+                  R *__restrict__ force)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    const int lane = threadIdx.x & 31;
+    R xi[D], Vi, vi[D];
+    loadXj<D, R>(xV, u32(i), xi, Vi);
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+    {
+        vi[a] = vel[i * D + a];
+        pos[i * D + a] += vi[a] * dt * R(0.5); // fluid_integration.hpp:167-170
+    }
+    R rate = R(0);
+    R pd[D];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        pd[a] = R(0);
+    {
+        const u32 cnt = in.count[i];
+        const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
+#pragma unroll 4
+        for (u32 k = 0; k < cnt; ++k)
+        {
+            u32 j = __ldg(lst + size_t(k) * 32u);
+            R xj[D], Vj, vj[D];
+            loadXj<D, R>(xV, j, xj, Vj);
+            loadVec<D, R>(vel, j, vj);
+            periodicImage<D, R>(xi, xj, per);
+            Pair<D, R> g;
+            pairGeometry<D, R>(xi, xj, kern, g);
+            R dWV = g.dW * Vj;
+            R u = R(0);
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+                u += (vi[a] - vj[a]) * g.e[a];
+            rate += u * dWV;
+            R pj = dissipativePJump<R>(fl, u) * dWV;
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+                pd[a] += pj * g.e[a];
+        }
+    }
+    const R rhoi = rho[i];
+    R dr = drho[i] + rate * rhoi;
+    R fo[D];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        fo[a] = pd[a] * Vi;
+    if (wall.n > 0)
+    {
+        R rw = R(0);
+        R pw[D];
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            pw[a] = R(0);
+        for (int t = 0; t < wall.n; ++t)
+        {
+            const TargetP<R> &T = wall.t[t];
+            const u32 cnt = T.count[i];
+            const u32 *lst = T.list + u64(T.slice_off[i >> 5]) * 32u + lane;
+            for (u32 k = 0; k < cnt; ++k)
+            {
+                u32 j = __ldg(lst + size_t(k) * 32u);
+                R xj[D], Vj, vw[D], nw[D];
+                loadXj<D, R>(T.xV, j, xj, Vj);
+                loadVec<D, R>(T.vel, j, vw);
+                loadVec<D, R>(T.nrm, j, nw);
+                Pair<D, R> g;
+                pairGeometry<D, R>(xi, xj, kern_w, g);
+                R dWV = g.dW * Vj;
+                R en = R(0);
+#pragma unroll
+                for (int a = 0; a < D; ++a)
+                    en += g.e[a] * nw[a];
+                R sgn = en < R(0) ? R(-1) : (en > R(0) ? R(1) : R(0)); // scalar_functions.h:127-131
+                R u1 = R(0), u2 = R(0);
+#pragma unroll
+                for (int a = 0; a < D; ++a)
+                {
+                    R v_in_wall = R(2.0) * vw[a] - vi[a];
+                    u1 += (vi[a] - v_in_wall) * g.e[a];
+                    u2 += (vi[a] - vw[a]) * (sgn * nw[a]);
+                }
+                rw += u1 * dWV;
+                R pj = dissipativePJump<R>(fl, R(2.0) * u2) * dWV;
+#pragma unroll
+                for (int a = 0; a < D; ++a)
+                    pw[a] += pj * (sgn * nw[a]);
+            }
+        }
+        dr += rw * rhoi;
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            fo[a] += pw[a] * Vi;
+    }
+    drho[i] = dr;
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        force[i * D + a] = fo[a];
+    rho[i] = rhoi + dr * dt * R(0.5); // fluid_integration.hpp:173-176
+}
+
+// ---------------------------------------------------------------------------------------------
+// time-step reductions and observables
+// ---------------------------------------------------------------------------------------------
+template <int D, class R>
+__global__ void __launch_bounds__(256)
+    k_acoustic_max(int64_t n, const R *__restrict__ vel, R c0, unsigned long long *__restrict__ slot)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    R s = R(0);
+    for (; i < n; i += int64_t(gridDim.x) * blockDim.x)
+    {
+        R v[D];
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            v[a] = vel[i * D + a];
+        s = fmax(s, c0 + sqrt_r(sqnormExact<D, R>(v)));
+    }
+    s = warpMax<R>(s);
+    if ((threadIdx.x & 31) == 0)
+        atomicMaxNonNeg(slot, double(s));
+}
+
+template <int D, class R>
+__global__ void __launch_bounds__(256)
+    k_advection_max(int64_t n, const R *__restrict__ vel, const R *__restrict__ force, const R *__restrict__ fprior,
+                    const R *__restrict__ mass, R h, unsigned long long *__restrict__ slot)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    R s = R(0);
+    for (; i < n; i += int64_t(gridDim.x) * blockDim.x)
+    {
+        R v[D], a[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d)
+        {
+            v[d] = vel[i * D + d];
+            a[d] = force[i * D + d] + fprior[i * D + d];
+        }
+        // fluid_time_step.cpp:54-59
+        R acc_scale = R(4.0) * h * sqrt_r(sqnormExact<D, R>(a)) / mass[i];
+        s = fmax(s, fmax(sqnormExact<D, R>(v), acc_scale));
+    }
+    s = warpMax<R>(s);
+    if ((threadIdx.x & 31) == 0)
+        atomicMaxNonNeg(slot, double(s));
+}
+
+// kind 0: total kinetic energy, 1: total mechanical energy (general_reduce.cpp:54-79), 2: max |v|
+template <int D, class R>
+__global__ void __launch_bounds__(256)
+    k_observable(int64_t n, int kind, const R *__restrict__ vel, const R *__restrict__ mass, const R *__restrict__ pos,
+                 R gx, R gy, R gz, double *__restrict__ partial)
+{
+    __shared__ double sh[8];
+    const R g[3] = {gx, gy, gz};
+    double s = 0.0;
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x)
+    {
+        R v[D];
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            v[a] = vel[i * D + a];
+        R v2 = sqnormExact<D, R>(v);
+        if (kind == 2)
+        {
+            s = fmax(s, double(sqrt_r(v2)));
+        }
+        else
+        {
+            R e = R(0.5) * mass[i] * v2;
+            if (kind == 1)
+            {
+                R pot = R(0);
+#pragma unroll
+                for (int a = 0; a < D; ++a)
+                    pot += g[a] * (R(0) - pos[i * D + a]);
+                e += mass[i] * pot;
+            }
+            s += double(e);
+        }
+    }
+    s = kind == 2 ? warpMax<double>(s) : warpSum<double>(s);
+    if ((threadIdx.x & 31) == 0)
+        sh[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        double t = sh[0];
+        for (int w = 1; w < 8; ++w)
+            t = kind == 2 ? fmax(t, sh[w]) : t + sh[w];
+        partial[blockIdx.x] = t;
+    }
+}
+__global__ void k_observable_final(int nb, int kind, const double *__restrict__ partial, double *__restrict__ out)
+{
+    if (threadIdx.x == 0 && blockIdx.x == 0)
+    {
+        double t = partial[0];
+        for (int b = 1; b < nb; ++b)
+            t = kind == 2 ? fmax(t, partial[b]) : t + partial[b];
+        *out = t;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// forces prior to the acoustic loop
+// ---------------------------------------------------------------------------------------------
+template <int D, class R>
+__global__ void __launch_bounds__(256)
+    k_gravity(int64_t n, const R *__restrict__ mass, R gx, R gy, R gz, R *__restrict__ cur, R *__restrict__ prev,
+              R *__restrict__ fprior)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    const R g[3] = {gx, gy, gz};
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+    {
+        R c = mass[i] * g[a];
+        cur[i * D + a] = c;
+        fprior[i * D + a] += c - prev[i * D + a]; // force_prior.hpp:22-26
+        prev[i * D + a] = c;
+    }
+}
+
+template <int D, class R>
+__global__ void __launch_bounds__(128)
+    k_viscous(int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, KernelP<R> kern,
+              PeriodicP<D, R> per, R mu, R h, const R *__restrict__ vel, R *__restrict__ vf, R *__restrict__ prev,
+              R *__restrict__ fprior)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    const int lane = threadIdx.x & 31;
+    R xi[D], Vi, vi[D];
+    loadXj<D, R>(xV, u32(i), xi, Vi);
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        vi[a] = vel[i * D + a];
+    const R mu_ij = R(2.0) * mu * mu * (R(1.0) / (mu + mu)); // particle_functors.h:163-177
+    R f[D];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        f[a] = R(0);
+    const u32 cnt = in.count[i];
+    const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
+#pragma unroll 2
+    for (u32 k = 0; k < cnt; ++k)
+    {
+        u32 j = __ldg(lst + size_t(k) * 32u);
+        R xj[D], Vj, vj[D];
+        loadXj<D, R>(xV, j, xj, Vj);
+        loadVec<D, R>(vel, j, vj);
+        periodicImage<D, R>(xi, xj, per);
+        Pair<D, R> g;
+        pairGeometry<D, R>(xi, xj, kern, g);
+        R ee = R(0);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            ee += g.e[a] * ((R(1.0) + R(1.0)) * g.e[a]); // e·(K_i+K_j)e with unit correction matrices
+        R c = ee * mu_ij * g.dW * Vj / (g.r + R(0.01) * h);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            f[a] += c * (vi[a] - vj[a]);
+    }
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+    {
+        R v = f[a] * Vi;
+        vf[i * D + a] = v;
+        fprior[i * D + a] += v - prev[i * D + a];
+        prev[i * D + a] = v;
+    }
+}
+
+template <int D, class R>
+__global__ void __launch_bounds__(128)
+    k_transport_velocity(int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, KernelP<R> kern,
+                         PeriodicP<D, R> per, R h2, R scaling, R *__restrict__ kgi, R *__restrict__ pos)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    const int lane = threadIdx.x & 31;
+    R xi[D], Vi;
+    loadXj<D, R>(xV, u32(i), xi, Vi);
+    R inc[D];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        inc[a] = R(0);
+    const u32 cnt = in.count[i];
+    const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
+#pragma unroll 2
+    for (u32 k = 0; k < cnt; ++k)
+    {
+        u32 j = __ldg(lst + size_t(k) * 32u);
+        R xj[D], Vj;
+        loadXj<D, R>(xV, j, xj, Vj);
+        periodicImage<D, R>(xi, xj, per);
+        Pair<D, R> g;
+        pairGeometry<D, R>(xi, xj, kern, g);
+        R c = (R(1.0) + R(1.0)) * g.dW * Vj;
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            inc[a] -= c * g.e[a];
+    }
+    R sq = R(0);
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+    {
+        kgi[i * D + a] = inc[a];
+        sq += inc[a] * inc[a];
+    }
+    R lim = fmin(R(100.0) * (h2 * sq), R(1)); // TruncatedLinear, slope 100 (common_functors.h:82-94)
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        pos[i * D + a] += scaling * lim * inc[a];
+}
+
+// ObservingAQuantity: out[i] = Σ W_ij V_j q_j / (Σ W_ij V_j + tiny)
+template <int D, class R>
+__global__ void __launch_bounds__(128)
+    k_observe(int64_t n, const typename Real4<R>::type *__restrict__ xV_obs, ContactP<R> ct, KernelP<R> kern,
+              const R *q0, const R *q1, const R *q2, const R *q3, int width, double *__restrict__ out)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    const int lane = threadIdx.x & 31;
+    const R *qs[kMaxTargets] = {q0, q1, q2, q3};
+    R xi[D], Vi;
+    loadXj<D, R>(xV_obs, u32(i), xi, Vi);
+    R acc[9];
+    for (int d = 0; d < 9; ++d)
+        acc[d] = R(0);
+    R w = R(0);
+    for (int t = 0; t < ct.n; ++t)
+    {
+        const TargetP<R> &T = ct.t[t];
+        const u32 cnt = T.count[i];
+        const u32 *lst = T.list + u64(T.slice_off[i >> 5]) * 32u + lane;
+        for (u32 k = 0; k < cnt; ++k)
+        {
+            u32 j = __ldg(lst + size_t(k) * 32u);
+            R xj[D], Vj;
+            loadXj<D, R>(T.xV, j, xj, Vj);
+            R r2 = R(0);
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+            {
+                R d = xi[a] - xj[a];
+                r2 += d * d;
+            }
+            R wj = kernelW<R>(sqrt_r(r2), kern) * Vj;
+            for (int d = 0; d < width; ++d)
+                acc[d] += wj * qs[t][size_t(j) * width + d];
+            w += wj;
+        }
+    }
+    for (int d = 0; d < width; ++d)
+        out[i * width + d] = double(acc[d] / (w + Tiny<R>::value));
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+template <class R>
+static ListP<R> listOf(const NeighborList &L)
+{
+    ListP<R> l;
+    l.count = L.count;
+    l.slice_off = L.slice_off;
+    l.list = L.list;
+    return l;
+}
+
+static sphb200_status checkRelation(sphb200_relation *r, bool want_inner, const char *who)
+{
+    sphb200_ctx *ctx = r->ctx;
+    if (r->inner != want_inner)
+        return ctx->fail(SPHB200_ERR_INVALID, std::string(who) + ": wrong relation kind");
+    if (!r->valid || r->source_stamp != r->body->config_stamp)
+        return ctx->fail(SPHB200_ERR_INVALID, std::string(who) + ": relation is stale (call relation_update after cell_list_update)");
+    for (size_t k = 0; k < r->targets.size(); ++k)
+        if (r->target_stamp[k] != r->targets[k]->config_stamp)
+            return ctx->fail(SPHB200_ERR_INVALID, std::string(who) + ": relation target was re-sorted; call relation_update");
+    return SPHB200_OK;
+}
+
+// need: bit 0 mass, 1 velocity, 2 acceleration, 3 normal
+template <int D, class R>
+static sphb200_status makeContactP(sphb200_relation *c, int need, ContactP<R> &out, KernelP<R> &kern_c)
+{
+    out.n = 0;
+    if (!c)
+        return SPHB200_OK;
+    sphb200_body *src = c->body;
+    out.n = int(c->targets.size());
+    kern_c = src->P<D, R>().kern;
+    for (int t = 0; t < out.n; ++t)
+    {
+        sphb200_body *tb = c->targets[size_t(t)];
+        SPHB_TRY((ensurePacked<D, R>(tb)));
+        TargetP<R> &T = out.t[t];
+        const NeighborList &L = c->lists[size_t(t)];
+        T.count = L.count;
+        T.slice_off = L.slice_off;
+        T.list = L.list;
+        T.xV = static_cast<const typename Real4<R>::type *>(tb->xV.p);
+        T.mass = T.vel = T.acc = T.nrm = nullptr;
+        R *ptr;
+        if (need & 1)
+        {
+            SPHB_TRY(getVarPtr<R>(tb, "Mass", 1, &ptr));
+            T.mass = ptr;
+        }
+        if (need & 2)
+        {
+            SPHB_TRY(getVarPtr<R>(tb, "Velocity", D, &ptr));
+            T.vel = ptr;
+        }
+        if (need & 4)
+        {
+            SPHB_TRY(getVarPtr<R>(tb, "Acceleration", D, &ptr));
+            T.acc = ptr;
+        }
+        if (need & 8)
+        {
+            SPHB_TRY(getVarPtr<R>(tb, "NormalDirection", D, &ptr));
+            T.nrm = ptr;
+        }
+        T.inv_rho0 = R(1.0) / R(tb->rho0);
+        if (tb->P<D, R>().h > kern_c.h)
+            kern_c = tb->P<D, R>().kern;
+    }
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status densitySummation(sphb200_relation *inner, sphb200_relation *contact, int free_surface)
+{
+    sphb200_ctx *ctx = inner->ctx;
+    sphb200_body *b = inner->body;
+    SPHB_TRY(checkRelation(inner, true, "density_summation"));
+    if (contact)
+        SPHB_TRY(checkRelation(contact, false, "density_summation"));
+    if (b->n == 0)
+        return SPHB200_OK;
+    BodyP<D, R> &P = b->P<D, R>();
+    SPHB_TRY((ensurePacked<D, R>(b)));
+    ContactP<R> ct;
+    KernelP<R> kern_ct = P.kern;
+    SPHB_TRY((makeContactP<D, R>(contact, 1, ct, kern_ct)));
+    R *mass, *rho_sum, *rho, *vol;
+    SPHB_TRY(getVarPtr<R>(b, "Mass", 1, &mass, true));
+    SPHB_TRY(getVarPtr<R>(b, "DensitySummation", 1, &rho_sum));
+    SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
+    SPHB_TRY(getVarPtr<R>(b, "VolumetricMeasure", 1, &vol, true));
+    auto *xV = static_cast<typename Real4<R>::type *>(b->xV.p);
+    k_density_summation<D, R><<<gridFor(b->n, 128), 128, 0, ctx->stream>>>(
+        b->n, xV, listOf<R>(inner->lists[0]), ct, P.kern, kern_ct, P.per, R(b->rho0), R(1.0) / P.sigma0, mass, rho_sum,
+        rho, vol, xV, free_surface);
+    SPHB_LAUNCH_CHECK(ctx);
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall, int riemann, double dt_)
+{
+    sphb200_ctx *ctx = inner->ctx;
+    sphb200_body *b = inner->body;
+    SPHB_TRY(checkRelation(inner, true, "integration_1st_half"));
+    if (wall)
+        SPHB_TRY(checkRelation(wall, false, "integration_1st_half"));
+    if (b->n == 0)
+        return SPHB200_OK;
+    BodyP<D, R> &P = b->P<D, R>();
+    SPHB_TRY((ensurePacked<D, R>(b)));
+    ContactP<R> wp;
+    KernelP<R> kern_w = P.kern;
+    SPHB_TRY((makeContactP<D, R>(wall, 4, wp, kern_w)));
+    FluidP<R> fl = makeFluidP<R>(b, P.h, riemann != 0);
+    R *rho, *p, *drho, *mass, *pos, *vel, *force, *fprior;
+    SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
+    SPHB_TRY(getVarPtr<R>(b, "Pressure", 1, &p, true));
+    SPHB_TRY(getVarPtr<R>(b, "DensityChangeRate", 1, &drho, true));
+    SPHB_TRY(getVarPtr<R>(b, "Mass", 1, &mass, true));
+    SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos, true));
+    SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel, true));
+    SPHB_TRY(getVarPtr<R>(b, "Force", D, &force, true));
+    SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
+    const R dt = R(dt_);
+    k_first_half_init<D, R><<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(b->n, dt, fl.p0, fl.rho0, rho, drho, p, pos, vel);
+    SPHB_LAUNCH_CHECK(ctx);
+    SPHB_TRY(reduceReset(ctx, 0, false));
+    k_first_half<D, R><<<gridFor(b->n, 128), 128, 0, ctx->stream>>>(
+        b->n, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), wp, P.kern, kern_w,
+        P.per, fl, dt, p, rho, mass, fprior, force, drho, vel, static_cast<unsigned long long *>(ctx->reduce_dev.p));
+    SPHB_LAUNCH_CHECK(ctx);
+    for (auto *ob : ctx->bodies)
+        ob->acoustic_max_valid = false;
+    b->acoustic_max_valid = true;
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall, int riemann, double dt_)
+{
+    sphb200_ctx *ctx = inner->ctx;
+    sphb200_body *b = inner->body;
+    SPHB_TRY(checkRelation(inner, true, "integration_2nd_half"));
+    if (wall)
+        SPHB_TRY(checkRelation(wall, false, "integration_2nd_half"));
+    if (b->n == 0)
+        return SPHB200_OK;
+    BodyP<D, R> &P = b->P<D, R>();
+    SPHB_TRY((ensurePacked<D, R>(b)));
+    ContactP<R> wp;
+    KernelP<R> kern_w = P.kern;
+    SPHB_TRY((makeContactP<D, R>(wall, 2 | 8, wp, kern_w)));
+    FluidP<R> fl = makeFluidP<R>(b, P.h, riemann != 0);
+    R *rho, *drho, *pos, *vel, *force;
+    SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
+    SPHB_TRY(getVarPtr<R>(b, "DensityChangeRate", 1, &drho, true));
+    SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos, true));
+    SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel, true));
+    SPHB_TRY(getVarPtr<R>(b, "Force", D, &force, true));
+    k_second_half<D, R><<<gridFor(b->n, 128), 128, 0, ctx->stream>>>(
+        b->n, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), wp, P.kern, kern_w,
+        P.per, fl, R(dt_), vel, pos, rho, drho, force);
+    SPHB_LAUNCH_CHECK(ctx);
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status acousticDt(sphb200_body *b, double cfl, double *dt_out)
+{
+    sphb200_ctx *ctx = b->ctx;
+    BodyP<D, R> &P = b->P<D, R>();
+    if (!b->acoustic_max_valid)
+    {
+        R *vel;
+        SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel, true));
+        SPHB_TRY(reduceReset(ctx, 0, false));
+        if (b->n > 0)
+        {
+            k_acoustic_max<D, R><<<148 * 4, 256, 0, ctx->stream>>>(b->n, vel, R(b->c0),
+                                                                  static_cast<unsigned long long *>(ctx->reduce_dev.p));
+            SPHB_LAUNCH_CHECK(ctx);
+        }
+    }
+    if (!dt_out)
+        return SPHB200_OK;
+    double m;
+    SPHB_TRY(reduceRead(ctx, 0, &m));
+    if (b->n == 0)
+        m = double(-std::numeric_limits<R>::max()); // reduce_functors.h:73-82 reference value MinReal
+    // fluid_time_step.cpp:27-31
+    *dt_out = double(R(cfl) * P.h / (R(m) + Tiny<R>::value));
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status advectionDt(sphb200_body *b, double U_ref, double cfl, int viscous, double *dt_out)
+{
+    sphb200_ctx *ctx = b->ctx;
+    BodyP<D, R> &P = b->P<D, R>();
+    R *vel, *force, *fprior, *mass;
+    SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel, true));
+    SPHB_TRY(getVarPtr<R>(b, "Force", D, &force, true));
+    SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
+    SPHB_TRY(getVarPtr<R>(b, "Mass", 1, &mass, true));
+    SPHB_TRY(reduceReset(ctx, 1, false));
+    if (b->n > 0)
+    {
+        k_advection_max<D, R><<<148 * 4, 256, 0, ctx->stream>>>(b->n, vel, force, fprior, mass, P.h,
+                                                               static_cast<unsigned long long *>(ctx->reduce_dev.p) + 1);
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    double m;
+    SPHB_TRY(reduceRead(ctx, 1, &m));
+    // fluid_time_step.cpp:61-79
+    R speed_ref = R(U_ref);
+    if (viscous)
+        speed_ref = std::max(R(b->mu) / R(b->rho0) / P.h, speed_ref);
+    R speed_max = std::sqrt(R(m));
+    if (dt_out)
+        *dt_out = double(R(cfl) * P.h / (std::max(speed_max, speed_ref) + Tiny<R>::value));
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status observable(sphb200_body *b, int kind, const double *g, double *out)
+{
+    sphb200_ctx *ctx = b->ctx;
+    R *vel, *mass, *pos;
+    SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel, true));
+    SPHB_TRY(getVarPtr<R>(b, "Mass", 1, &mass, true));
+    SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos, true));
+    const int nb = 148 * 2;
+    SPHB_CUDA(ctx, ctx->scratch_a.ensure(size_t(nb + 1) * 8));
+    double *partial = static_cast<double *>(ctx->scratch_a.p);
+    k_observable<D, R><<<nb, 256, 0, ctx->stream>>>(b->n, kind, vel, mass, pos, g ? R(g[0]) : R(0), g ? R(g[1]) : R(0),
+                                                    (g && D == 3) ? R(g[2]) : R(0), partial);
+    SPHB_LAUNCH_CHECK(ctx);
+    k_observable_final<<<1, 32, 0, ctx->stream>>>(nb, kind, partial, partial + nb);
+    SPHB_LAUNCH_CHECK(ctx);
+    SPHB_CUDA(ctx, cudaMemcpyAsync(ctx->reduce_host, partial + nb, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *out = *static_cast<double *>(ctx->reduce_host);
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status gravityForce(sphb200_body *b, const double *g)
+{
+    sphb200_ctx *ctx = b->ctx;
+    if (b->n == 0)
+        return SPHB200_OK;
+    R *mass, *cur, *prev, *fprior;
+    SPHB_TRY(getVarPtr<R>(b, "Mass", 1, &mass, true));
+    SPHB_TRY(getVarPtr<R>(b, "GravityForce", D, &cur));
+    SPHB_TRY(getVarPtr<R>(b, "PreviousGravityForce", D, &prev, true));
+    SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
+    k_gravity<D, R><<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(b->n, mass, R(g[0]), R(g[1]), D == 3 ? R(g[2]) : R(0),
+                                                               cur, prev, fprior);
+    SPHB_LAUNCH_CHECK(ctx);
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status viscousForce(sphb200_relation *inner)
+{
+    sphb200_ctx *ctx = inner->ctx;
+    sphb200_body *b = inner->body;
+    SPHB_TRY(checkRelation(inner, true, "viscous_force"));
+    if (b->n == 0)
+        return SPHB200_OK;
+    BodyP<D, R> &P = b->P<D, R>();
+    SPHB_TRY((ensurePacked<D, R>(b)));
+    R *vel, *vf, *prev, *fprior;
+    SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel, true));
+    SPHB_TRY(getVarPtr<R>(b, "ViscousForce", D, &vf));
+    SPHB_TRY(getVarPtr<R>(b, "PreviousViscousForce", D, &prev, true));
+    SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
+    k_viscous<D, R><<<gridFor(b->n, 128), 128, 0, ctx->stream>>>(
+        b->n, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), P.kern, P.per,
+        R(b->mu), P.h, vel, vf, prev, fprior);
+    SPHB_LAUNCH_CHECK(ctx);
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status transportVelocity(sphb200_relation *inner, double coefficient)
+{
+    sphb200_ctx *ctx = inner->ctx;
+    sphb200_body *b = inner->body;
+    SPHB_TRY(checkRelation(inner, true, "transport_velocity_correction"));
+    if (b->n == 0)
+        return SPHB200_OK;
+    BodyP<D, R> &P = b->P<D, R>();
+    SPHB_TRY((ensurePacked<D, R>(b)));
+    R *kgi, *pos;
+    SPHB_TRY(getVarPtr<R>(b, "KernelGradientIntegral", D, &kgi));
+    SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos, true));
+    R h2 = P.h * P.h;
+    k_transport_velocity<D, R><<<gridFor(b->n, 128), 128, 0, ctx->stream>>>(
+        b->n, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), P.kern, P.per, h2,
+        R(coefficient) * h2, kgi, pos);
+    SPHB_LAUNCH_CHECK(ctx);
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status observe(sphb200_relation *contact, const char *name, int width, double *out)
+{
+    sphb200_ctx *ctx = contact->ctx;
+    sphb200_body *b = contact->body;
+    SPHB_TRY(checkRelation(contact, false, "observe"));
+    if (b->n == 0)
+        return SPHB200_OK;
+    SPHB_TRY((ensurePacked<D, R>(b)));
+    ContactP<R> ct;
+    KernelP<R> kern = b->P<D, R>().kern;
+    SPHB_TRY((makeContactP<D, R>(contact, 0, ct, kern)));
+    const R *q[kMaxTargets] = {nullptr, nullptr, nullptr, nullptr};
+    for (int t = 0; t < ct.n; ++t)
+    {
+        R *ptr;
+        Var *v = contact->targets[size_t(t)]->find(name);
+        if (!v)
+            return ctx->fail(SPHB200_ERR_NOT_FOUND, std::string("observe: variable '") + name + "' not registered on target");
+        SPHB_TRY(getVarPtr<R>(contact->targets[size_t(t)], name, width, &ptr));
+        q[t] = ptr;
+    }
+    SPHB_CUDA(ctx, ctx->scratch_a.ensure(size_t(b->n) * size_t(width) * 8));
+    double *dev_out = static_cast<double *>(ctx->scratch_a.p);
+    k_observe<D, R><<<gridFor(b->n, 128), 128, 0, ctx->stream>>>(
+        b->n, static_cast<const typename Real4<R>::type *>(b->xV.p), ct, kern, q[0], q[1], q[2], q[3], width, dev_out);
+    SPHB_LAUNCH_CHECK(ctx);
+    SPHB_CUDA(ctx, cudaMemcpyAsync(out, dev_out, size_t(b->n) * size_t(width) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return SPHB200_OK;
+}
+} // namespace sphb
+
+extern "C"
+{
+sphb200_status sphb200_density_summation(sphb200_relation *inner, sphb200_relation *contact, int free_surface)
+{
+    if (!inner)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(inner->ctx->device);
+    return SPHB_DISPATCH(inner->ctx, densitySummation, inner, contact, free_surface);
+}
+sphb200_status sphb200_integration_1st_half(sphb200_relation *inner, sphb200_relation *wall, int riemann, double dt)
+{
+    if (!inner)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(inner->ctx->device);
+    return SPHB_DISPATCH(inner->ctx, firstHalf, inner, wall, riemann, dt);
+}
+sphb200_status sphb200_integration_2nd_half(sphb200_relation *inner, sphb200_relation *wall, int riemann, double dt)
+{
+    if (!inner)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(inner->ctx->device);
+    return SPHB_DISPATCH(inner->ctx, secondHalf, inner, wall, riemann, dt);
+}
+sphb200_status sphb200_acoustic_dt(sphb200_body *b, double cfl, double *dt_out)
+{
+    if (!b)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, acousticDt, b, cfl, dt_out);
+}
+sphb200_status sphb200_advection_dt(sphb200_body *b, double U_ref, double cfl, int viscous, double *dt_out)
+{
+    if (!b)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, advectionDt, b, U_ref, cfl, viscous, dt_out);
+}
+sphb200_status sphb200_gravity_force(sphb200_body *b, const double *g)
+{
+    if (!b || !g)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, gravityForce, b, g);
+}
+sphb200_status sphb200_viscous_force(sphb200_relation *inner)
+{
+    if (!inner)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(inner->ctx->device);
+    return SPHB_DISPATCH(inner->ctx, viscousForce, inner);
+}
+sphb200_status sphb200_transport_velocity_correction(sphb200_relation *inner, double coefficient)
+{
+    if (!inner)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(inner->ctx->device);
+    return SPHB_DISPATCH(inner->ctx, transportVelocity, inner, coefficient);
+}
+sphb200_status sphb200_total_kinetic_energy(sphb200_body *b, double *out)
+{
+    if (!b || !out)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, observable, b, 0, nullptr, out);
+}
+sphb200_status sphb200_total_mechanical_energy(sphb200_body *b, const double *g, double *out)
+{
+    if (!b || !out || !g)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, observable, b, 1, g, out);
+}
+sphb200_status sphb200_maximum_speed(sphb200_body *b, double *out)
+{
+    if (!b || !out)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, observable, b, 2, nullptr, out);
+}
+sphb200_status sphb200_observe(sphb200_relation *contact, const char *name, int width, double *out)
+{
+    if (!contact || !name || !out || width < 1 || width > 9)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(contact->ctx->device);
+    return SPHB_DISPATCH(contact->ctx, observe, contact, name, width, out);
+}
+} // extern "C"

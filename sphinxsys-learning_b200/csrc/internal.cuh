@@ -1,0 +1,413 @@
+// Internal types of libsphb200: context / body / relation objects behind the opaque C handles,
+// device-side parameter PODs, Wendland-C2 helpers and the (ndim, Real) dispatch.
+#pragma once
+#include "../../include/sphb200.h"
+#include <cuda_runtime.h>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+namespace sphb
+{
+typedef uint32_t u32;
+typedef uint64_t u64;
+
+constexpr int kMaxTargets = 4;
+constexpr double kPi = 3.14159265358979323846;
+
+// common/base_data_type.h:207 TinyReal
+template <class R>
+struct Tiny
+{
+    static constexpr R value = R(2.71051e-20);
+};
+
+template <class R>
+struct Real4;
+template <>
+struct Real4<float>
+{
+    typedef float4 type;
+};
+template <>
+struct Real4<double>
+{
+    typedef double4 type;
+};
+
+// ---------------------------------------------------------------------------------------------
+// Device-side parameter blocks (passed by value to kernels)
+// ---------------------------------------------------------------------------------------------
+// meshes/base_mesh.cpp:6-16, base_mesh.hxx:9-15,68-78
+template <int D, class R>
+struct MeshP
+{
+    R lo[D];
+    R spacing;
+    int cells[D];
+
+    __host__ __device__ inline void cellIndex(const R *pos, int *c) const
+    {
+#pragma unroll
+        for (int d = 0; d < D; ++d)
+        {
+            int v = int(floor((pos[d] - lo[d]) / spacing));
+            v = v < 0 ? 0 : v;
+            v = v > cells[d] - 1 ? cells[d] - 1 : v;
+            c[d] = v;
+        }
+    }
+    // x slowest, last axis fastest
+    __host__ __device__ inline u32 linear(const int *c) const
+    {
+        if (D == 2)
+            return u32(c[0]) * u32(cells[1]) + u32(c[1]);
+        return (u32(c[0]) * u32(cells[1]) + u32(c[1])) * u32(cells[D - 1]) + u32(c[D - 1]);
+    }
+    __host__ __device__ inline u64 total() const
+    {
+        u64 n = 1;
+        for (int d = 0; d < D; ++d)
+            n *= u64(cells[d]);
+        return n;
+    }
+};
+
+// kernels/kernel_wendland_c2.cpp:8-35, base_kernel.cpp:6-27
+template <class R>
+struct KernelP
+{
+    R h, inv_h, rc, rc2, factor_W, factor_dW;
+};
+
+template <int D, class R>
+struct PeriodicP
+{
+    int mask; // bit a set: axis a periodic
+    R lo[D], hi[D], L[D], half_L[D];
+};
+
+// everything (D,R)-typed that a body owns on the host side
+template <int D, class R>
+struct BodyP
+{
+    R dp, h;
+    KernelP<R> kern;
+    R sigma0;
+    MeshP<D, R> mesh;
+    PeriodicP<D, R> per;
+};
+
+// SELL-32 neighbour list of one (source, target) pair: particle i = 32*s + lane stores its k-th
+// neighbour at list[32*(slice_off[s] + k) + lane]; count[i] entries are valid.
+struct NeighborList
+{
+    u32 *count = nullptr;     // [n_src]
+    u32 *slice_w = nullptr;   // [n_slices]  max count in the slice
+    u32 *slice_off = nullptr; // [n_slices+1] exclusive scan of slice_w (units of 32 entries)
+    u32 *list = nullptr;
+    size_t cap_entries = 0, cap_src = 0;
+    u64 total_entries = 0; // 32 * slice_off[n_slices]
+    u64 total_pairs = 0;
+};
+
+// per-target device pointers handed to the interaction kernels
+template <class R>
+struct TargetP
+{
+    const u32 *count;
+    const u32 *slice_off;
+    const u32 *list;
+    const typename Real4<R>::type *xV; // frozen position + Vol of the target body
+    const R *mass, *vel, *acc, *nrm;
+    R inv_rho0;
+};
+template <class R>
+struct ContactP
+{
+    int n;
+    TargetP<R> t[kMaxTargets];
+};
+
+// ---------------------------------------------------------------------------------------------
+// Host objects
+// ---------------------------------------------------------------------------------------------
+struct DevBuf
+{
+    void *p = nullptr;
+    size_t bytes = 0;
+    cudaError_t ensure(size_t need, bool keep = false, cudaStream_t st = 0);
+    void release();
+};
+
+struct Var
+{
+    std::string name;
+    int width = 1;
+    bool evolving = false;
+    void *host = nullptr;
+    DevBuf dev;
+};
+} // namespace sphb
+
+struct sphb200_ctx
+{
+    int device = 0, ndim = 3, real_bytes = 8;
+    double sys_lo[3] = {0, 0, 0}, sys_hi[3] = {0, 0, 0};
+    cudaStream_t stream = nullptr;
+    std::string error;
+    int64_t launches = 0;
+    std::vector<sphb200_body *> bodies;
+    std::vector<sphb200_relation *> relations;
+    sphb::DevBuf scratch_a, scratch_b, scan_tmp, reduce_dev;
+    void *reduce_host = nullptr; // pinned, 64 doubles
+
+    sphb200_status fail(sphb200_status s, const std::string &msg)
+    {
+        error = msg;
+        return s;
+    }
+};
+
+struct sphb200_body
+{
+    sphb200_ctx *ctx = nullptr;
+    std::string name;
+    int64_t n = 0;
+    double dp = 0, h_ratio = 1.3;
+    // material
+    double rho0 = 1, c0 = 1, mu = 0, youngs = 0, poisson = 0, K0 = 0, G0 = 0, lambda0 = 0, cs0 = 0;
+    bool periodic[3] = {false, false, false};
+    double per_lo[3] = {0, 0, 0}, per_hi[3] = {0, 0, 0};
+    alignas(16) unsigned char params[512]; // BodyP<D,R>
+    std::map<std::string, std::unique_ptr<sphb::Var>> vars;
+    sphb::DevBuf original_id, sorted_id;            // u32[n]
+    sphb::DevBuf cell_of, rank_in_cell, perm;        // u32[n]
+    sphb::DevBuf cell_count, cell_offset;            // u32[cells+1]
+    sphb::DevBuf xV;                                 // Real4[n]: frozen position + Vol
+    sphb::DevBuf tmp_var;                            // permutation double buffer
+    int64_t n_cells = 0;
+    bool cell_list_valid = false;
+    bool xV_vol_dirty = true; // Vol component of xV must be refreshed before the next interaction
+    uint64_t config_stamp = 0;
+    bool acoustic_max_valid = false; // reduce slot 0 holds max(c0+|v|) from the last 1st half
+
+    template <int D, class R>
+    sphb::BodyP<D, R> &P() { return *reinterpret_cast<sphb::BodyP<D, R> *>(params); }
+    sphb::Var *find(const char *nm)
+    {
+        auto it = vars.find(nm);
+        return it == vars.end() ? nullptr : it->second.get();
+    }
+};
+
+struct sphb200_relation
+{
+    sphb200_ctx *ctx = nullptr;
+    sphb200_body *body = nullptr;
+    bool inner = true;
+    std::vector<sphb200_body *> targets; // inner: {body}
+    std::vector<sphb::NeighborList> lists;
+    std::vector<uint64_t> target_stamp;
+    uint64_t source_stamp = 0;
+    bool valid = false;
+};
+
+namespace sphb
+{
+// ---------------------------------------------------------------------------------------------
+// error helpers
+// ---------------------------------------------------------------------------------------------
+#define SPHB_CUDA(ctx, expr)                                                                                     \
+    do                                                                                                           \
+    {                                                                                                            \
+        cudaError_t _e = (expr);                                                                                 \
+        if (_e != cudaSuccess)                                                                                   \
+            return (ctx)->fail(SPHB200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e) + " at " +   \
+                                                     __FILE__ + ":" + std::to_string(__LINE__));                 \
+    } while (0)
+
+#define SPHB_TRY(expr)               \
+    do                               \
+    {                                \
+        sphb200_status _s = (expr);  \
+        if (_s != SPHB200_OK)        \
+            return _s;               \
+    } while (0)
+
+#define SPHB_LAUNCH_CHECK(ctx)                  \
+    do                                          \
+    {                                           \
+        (ctx)->launches++;                      \
+        SPHB_CUDA(ctx, cudaGetLastError());     \
+    } while (0)
+
+// dispatch a templated implementation on the context's (ndim, real_bytes)
+#define SPHB_DISPATCH(ctx, FN, ...)                                         \
+    ((ctx)->ndim == 3 ? ((ctx)->real_bytes == 8 ? FN<3, double>(__VA_ARGS__) \
+                                                : FN<3, float>(__VA_ARGS__)) \
+                      : ((ctx)->real_bytes == 8 ? FN<2, double>(__VA_ARGS__) \
+                                                : FN<2, float>(__VA_ARGS__)))
+
+inline int gridFor(int64_t n, int block) { return int((n + block - 1) / block); }
+
+// variable lookup with auto-registration (mirrors registerStateVariable's create-if-missing)
+sphb200_status getVar(sphb200_body *b, const char *name, int width, bool evolving, Var **out);
+template <class R>
+inline sphb200_status getVarPtr(sphb200_body *b, const char *name, int width, R **out, bool evolving = false)
+{
+    Var *v = nullptr;
+    SPHB_TRY(getVar(b, name, width, evolving, &v));
+    *out = static_cast<R *>(v->dev.p);
+    return SPHB200_OK;
+}
+
+// device scan of n u32 (exclusive); out may alias in.  Total written to out[n] when with_total.
+sphb200_status exclusiveScanU32(sphb200_ctx *ctx, const u32 *in, u32 *out, int64_t n, bool with_total);
+
+// refresh the Vol component of xV (and nothing else) if a dynamics changed VolumetricMeasure
+template <int D, class R>
+sphb200_status ensurePacked(sphb200_body *b);
+
+// reduction slots (device u64 bit patterns of non-negative doubles)
+sphb200_status reduceReset(sphb200_ctx *ctx, int slot, bool for_min);
+sphb200_status reduceRead(sphb200_ctx *ctx, int slot, double *out);
+
+// ---------------------------------------------------------------------------------------------
+// device helpers
+// ---------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double rsqrt_r(double a) { return rsqrt(a); }
+__device__ __forceinline__ float rsqrt_r(float a) { return rsqrtf(a); }
+__device__ __forceinline__ double sqrt_r(double a) { return sqrt(a); }
+__device__ __forceinline__ float sqrt_r(float a) { return sqrtf(a); }
+
+// squaredNorm evaluated exactly as the CPU path does: products and left-to-right sums, no FMA
+template <int D, class R>
+__device__ __forceinline__ R sqnormExact(const R *d)
+{
+    R s = mul_rn(d[0], d[0]);
+#pragma unroll
+    for (int k = 1; k < D; ++k)
+        s = add_rn(s, mul_rn(d[k], d[k]));
+    return s;
+}
+
+// read-only 16/32-byte record load (double4 has no __ldg overload: two 16-byte halves)
+__device__ __forceinline__ float4 ldg4(const float4 *p) { return __ldg(p); }
+__device__ __forceinline__ double4 ldg4(const double4 *p)
+{
+    const double2 *q = reinterpret_cast<const double2 *>(p);
+    double2 a = __ldg(q), b = __ldg(q + 1);
+    return make_double4(a.x, a.y, b.x, b.y);
+}
+
+template <class R>
+__device__ __forceinline__ void loadX(const typename Real4<R>::type *p, u32 i, R *x, R &w)
+{
+    typename Real4<R>::type v = ldg4(p + i);
+    x[0] = v.x;
+    x[1] = v.y;
+    x[2] = v.z;
+    w = v.w;
+}
+
+// Pair geometry recomputed from the frozen positions.  r = |d|, e = d/r (0 when r == 0, as
+// d/(r+TinyReal) gives), dW per kernel_wendland_c2.cpp:28-35, W per :17-26.
+template <int D, class R>
+struct Pair
+{
+    R e[D];
+    R r, dW;
+};
+template <int D, class R>
+__device__ __forceinline__ void pairGeometry(const R *xi, const R *xj, const KernelP<R> &k, Pair<D, R> &g)
+{
+    R d[D];
+    R r2 = R(0);
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+    {
+        d[a] = xi[a] - xj[a];
+        r2 += d[a] * d[a];
+    }
+    R rinv = r2 > R(0) ? rsqrt_r(r2) : R(0);
+    g.r = r2 * rinv;
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        g.e[a] = d[a] * rinv;
+    R q = g.r * k.inv_h;
+    R t = q - R(2.0);
+    g.dW = k.factor_dW * (R(0.625) * (t * t * t) * q);
+}
+template <class R>
+__device__ __forceinline__ R kernelW(R r, const KernelP<R> &k)
+{
+    R q = r * k.inv_h;
+    R t = R(1.0) - R(0.5) * q;
+    R t2 = t * t;
+    return k.factor_W * ((t2 * t2) * (R(1.0) + R(2.0) * q));
+}
+
+// minimum-image translation of x_j for periodic axes (reproduces the ghost copy x_j ± L that the
+// reference inserts into the cell lists: domain_bounding.cpp:18-65)
+template <int D, class R>
+__device__ __forceinline__ void periodicImage(const R *xi, R *xj, const PeriodicP<D, R> &per)
+{
+    if (per.mask == 0)
+        return;
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        if (per.mask & (1 << a))
+        {
+            R t = xi[a] - xj[a];
+            if (t > per.half_L[a])
+                xj[a] = xj[a] + per.L[a];
+            else if (t < -per.half_L[a])
+                xj[a] = xj[a] - per.L[a];
+        }
+}
+
+__device__ __forceinline__ void atomicMaxNonNeg(unsigned long long *slot, double v)
+{
+    atomicMax(slot, (unsigned long long)__double_as_longlong(v));
+}
+__device__ __forceinline__ void atomicMinNonNeg(unsigned long long *slot, double v)
+{
+    atomicMin(slot, (unsigned long long)__double_as_longlong(v));
+}
+template <class R>
+__device__ __forceinline__ R warpMax(R v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+template <class R>
+__device__ __forceinline__ R warpMin(R v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+template <class R>
+__device__ __forceinline__ R warpSum(R v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+#endif // __CUDACC__
+} // namespace sphb
