@@ -1,0 +1,265 @@
+#!/usr/bin/env python
+"""bench.py - particle-steps/s of the WCSPH particle-interaction path on the 3-D dam break.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--dp DP] [--real 8|4] [--impl reference]
+
+A bench "step" is one advection step of the reference's main loop (tests/3d_examples/test_3d_dambreak/
+dambreak.cpp:159-195): advection dt, density summation, the acoustic sub-step loop (Integration1stHalf +
+Integration2ndHalf + AcousticTimeStep), then cell-list/sort and Inner+Contact relation updates.  The
+metric is particle-steps/s = N_fluid * (#acoustic sub-steps) / time, everything else
+amortised.  One JSON line on stdout (rank 0).
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+METRIC = "particle-steps/sec, 3D dambreak WCSPH"
+UNIT = "particle-steps/s"
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled every 200 ms during the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "200"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.p.terminate()
+        self.p.wait()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.f.name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_run(dp, steps, warmup):
+    """the reference algorithm on the host cores: the CPU restatement (oracle, kind "port") - the TBB
+    build of the reference cannot be compiled in this image (no Eigen/TBB/Boost/Simbody)."""
+    pk = importlib.import_module("sphinxsys-learning_b200")
+    from oracle import binding as oracle
+    c = pk.cases.DamBreak(oracle, ndim=3, dp=dp, real_bytes=8, with_observer=False)
+    for _ in range(warmup):
+        c.advection_step()
+    n0 = c.n_acoustic
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        c.advection_step()
+    dt = time.perf_counter() - t0
+    sub = c.n_acoustic - n0
+    return {"value": c.water.n * sub / dt, "unit": UNIT, "cores": int(oracle.load().orc_num_threads()), "kind": "port",
+            "sample": f"3-D dam break dp={dp:g}: {c.water.n} fluid + {c.wall.n} wall particles, {steps} advection steps "
+                      f"({sub} acoustic sub-steps) in {dt:.1f} s, OpenMP CPU restatement of the classic stored-neighbourhood algorithm"}, dt / max(steps, 1)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=6)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--dp", type=float, default=1.0 / 272.0, help="particle spacing (1/272 -> 20 123 648 fluid particles)")
+    ap.add_argument("--real", type=int, default=8, choices=[4, 8], help="bytes per Real (8 = the reference's default build)")
+    ap.add_argument("--impl", default="sphb200", choices=["sphb200", "reference"])
+    ap.add_argument("--cpu-dp", type=float, default=1.0 / 96.0, help="spacing of the bounded CPU-baseline sample (1/96 -> 884 736 fluid particles)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    warmup = max(a.warmup, 3)
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        base, ms = cpu_reference_run(a.cpu_dp, max(a.steps, 1), 1)
+        print(json.dumps({"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": a.gpus,
+                          "steps": a.steps, "warmup": 1, "ms_per_step": ms * 1e3, "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                          "config": {"workload": "test_3d_dambreak lattice, bounded CPU sample", "dp": a.cpu_dp},
+                          "cpu_baseline": base,
+                          "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    pk = importlib.import_module("sphinxsys-learning_b200")
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+
+    # ---- build the case (every rank holds one slab-sized copy of the workload: weak scaling) ----
+    t_build = time.perf_counter()
+    case = pk.cases.DamBreak(pk.host, ndim=3, dp=a.dp, real_bytes=a.real, with_observer=True, device=local_rank,
+                             stream=stream.cuda_stream)
+    S, w = case.sys, case.water
+    t_build = time.perf_counter() - t_build
+    n_f, n_w = w.n, case.wall.n
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- `value`: state resident in HBM ---------------------------------------------------------
+    for _ in range(warmup):
+        case.advection_step()
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    launches0, sub0 = S.launches, case.n_acoustic
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(a.steps):
+        case.advection_step()
+    ev1.record(stream)
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    ms = ev0.elapsed_time(ev1)
+    sub = case.n_acoustic - sub0
+    launches = S.launches - launches0
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = world * n_f * sub / (ms_max * 1e-3)
+
+    # ---- roofline of the dominant kernel (Integration2ndHalf: one launch per call) ---------------
+    counts_in = case.inner.neighbors()[0]
+    counts_w = case.wall_contact.neighbors()[0]
+    pairs_in, pairs_w = int(counts_in.sum()), int(counts_w.sum())
+    R = a.real
+    fields_B = 20 * R  # K3 of SURVEY §8d: 160 B fp64 / 80 B fp32 per particle
+    alg_bytes = n_f * fields_B + 4 * (pairs_in + pairs_w)
+    reps = 5
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    S.integration_2nd_half(case.inner, case.wall_contact, True, 0.0)
+    torch.cuda.synchronize()
+    k0.record(stream)
+    for _ in range(reps):
+        S.integration_2nd_half(case.inner, case.wall_contact, True, 0.0)
+    k1.record(stream)
+    torch.cuda.synchronize()
+    k_ms = k0.elapsed_time(k1) / reps
+    peak, peak_src = peaks()
+    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_second_half (Integration2ndHalf inner+wall, fused init/update)",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg_bytes,
+                "pairs_per_particle": (pairs_in + pairs_w) / n_f}
+    a_step = 56 * R + 2 * 4 * (pairs_in + pairs_w) / n_f  # SURVEY §8d A_step: 448/224 B fields + 2 list reads
+    step_frac = a_step * value / world / 1e9 / peak
+
+    # ---- `e2e`: host buffers in, observables out, every step ------------------------------------
+    e2e = None
+    if not a.no_e2e:
+        names = [n for n in ("Position", "Velocity", "Density", "Pressure", "DensityChangeRate", "Force", "ForcePrior",
+                             "Mass", "VolumetricMeasure")]
+        host = {}
+        for nm in names:
+            arr = w.get(nm)
+            pinned = torch.from_numpy(arr).pin_memory()
+            host[nm] = pinned
+        h2d = sum(v.numel() * v.element_size() for v in host.values())
+        lib = S.lib
+        import ctypes as C
+
+        def e2e_step():
+            for nm, ten in host.items():
+                S.check(lib.sphb200_var_upload(w.h, nm.encode(), C.c_void_p(ten.data_ptr())))
+            # host arrays define the particle order: rebuild cell list + configuration as the
+            # reference does after a reload (Dambreak.cpp:132-138)
+            w.update_cell_list()
+            case.update_configuration()
+            case.advection_step()
+            e = case.mechanical_energy()
+            p = case.probe_pressure()
+            # hand the advanced state back to the host arrays (all of them: the step re-sorted the body)
+            for nm, ten in host.items():
+                S.check(lib.sphb200_var_download(w.h, nm.encode(), C.c_void_p(ten.data_ptr())))
+            return e, p
+
+        e2e_step()
+        barrier()
+        sub0 = case.n_acoustic
+        t0 = time.perf_counter()
+        ev0.record(stream)
+        for _ in range(a.steps):
+            e2e_step()
+        ev1.record(stream)
+        barrier()
+        ms_e = max(ev0.elapsed_time(ev1), (time.perf_counter() - t0) * 1e3)
+        t = torch.tensor([ms_e], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        sub_e = case.n_acoustic - sub0
+        e2e = {"value": world * n_f * sub_e / (float(t.item()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(h2d + 8 + 8 * 6 + 8 * (sub_e // max(a.steps, 1) + 1)),
+               "note": "host-resident state: every step uploads the evolving fluid state from pinned host arrays "
+                       "(sphb200_var_upload), rebuilds cell list + relations, runs one advection step, reads back energy, "
+                       "probe pressures, the dt values and the whole state (sphb200_var_download)"}
+
+    cpu_base = None
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        cpu_base, _ = cpu_reference_run(a.cpu_dp, 4, 1)
+
+    if rank == 0:
+        out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": warmup,
+               "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+               "dtype": "f64" if R == 8 else "f32", "data": "synthetic",
+               "config": {"workload": f"test_3d_dambreak lattice dp={a.dp:.6g}: {n_f} fluid + {n_w} wall particles per GPU",
+                          "acoustic_substeps": sub, "advection_steps": a.steps, "l2": "inputs larger than L2",
+                          "parallelism": "1 slab per GPU" if world > 1 else "single GPU", "build_seconds": round(t_build, 1)},
+               "roofline": roofline, "step_roofline_frac": step_frac, "a_step_bytes": a_step,
+               "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -157,14 +157,22 @@ sphb200_status sphb200_solid_dt(sphb200_body *b, double cfl, double *dt_out);
 sphb200_status sphb200_exclusive_scan_u32(sphb200_ctx *ctx, const uint32_t *in, uint32_t *out, int64_t n, uint64_t *total);
 
 /* ---- slab decomposition helpers (multi-GPU; no reference equivalent) ------------ */
-/* gather rows `idx[0..m)` (current order) of variable `name` into a packed device buffer / scatter back */
-sphb200_status sphb200_var_gather(sphb200_body *b, const char *name, const int64_t *idx_dev, int64_t m, void *dst_dev);
-sphb200_status sphb200_var_scatter(sphb200_body *b, const char *name, const int64_t *idx_dev, int64_t m, const void *src_dev);
-/* change the number of particles (migration in/out); keeps the first min(n_old,n_new) rows */
+/* enqueue all further work of this context on the caller's cudaStream_t (e.g. torch's current
+ * stream, so that torch.distributed collectives and these kernels are ordered without host syncs) */
+sphb200_status sphb200_ctx_set_stream(sphb200_ctx *ctx, void *cuda_stream);
+/* change the number of particles (migration in/out, halo rebuild); keeps the first
+ * min(n_old, n_new) rows of every variable, zero-fills the rest, resets OriginalID/SortedID to iota
+ * and invalidates the cell list.  Device pointers obtained earlier are invalid afterwards. */
 sphb200_status sphb200_body_resize(sphb200_body *b, int64_t n_new);
-/* particles [n_owned, n) are ghosts: they take part as neighbours j but are skipped as i by the
- * dynamics and reductions (their state is refreshed by the halo exchange) */
-sphb200_status sphb200_body_set_owned(sphb200_body *b, int64_t n_owned);
+/* this rank owns the cell pages [page_lo, page_hi) along axis 0 (the slowest index of the linear cell
+ * index, base_mesh.hxx:68-78, so a slab is a contiguous range of the cell-sorted particles).  After
+ * the next cell_list_update the dynamics and reductions visit only the owned particles as i; all
+ * particles (owned + halo copies) serve as neighbours j.  page_lo < 0 restores "own everything". */
+sphb200_status sphb200_body_set_owned_pages(sphb200_body *b, int page_lo, int page_hi);
+/* [begin, end) of the owned particles in the current (cell-sorted) order */
+sphb200_status sphb200_body_owned_range(sphb200_body *b, int64_t *begin, int64_t *end);
+/* device pointers of the u32 OriginalID / SortedID arrays (valid until the next resize) */
+sphb200_status sphb200_ids_device_ptr(sphb200_body *b, void **original_id, void **sorted_id);
 
 #ifdef __cplusplus
 }

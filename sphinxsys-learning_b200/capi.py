@@ -1,0 +1,97 @@
+"""ctypes binding of the C ABI declared in include/sphb200.h.
+
+The library is the product: if libsphb200.so is missing or no CUDA device is present this module
+raises - there is no CPU fallback (the CPU oracle lives under oracle/ and is test infrastructure only).
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsphb200.so")
+
+OK, ERR_INVALID, ERR_CUDA, ERR_NOT_FOUND, ERR_NO_DEVICE = range(5)
+
+
+class SphB200Error(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(f"sphb200 status {status}: {message}")
+        self.status = status
+
+
+_lib = None
+
+_vp, _i, _i64, _d, _cp = C.c_void_p, C.c_int, C.c_int64, C.c_double, C.c_char_p
+_dp = C.POINTER(C.c_double)
+_i64p = C.POINTER(C.c_int64)
+_vpp = C.POINTER(C.c_void_p)
+
+# name -> (restype, argtypes); every symbol include/sphb200.h declares
+SIGNATURES = {
+    "sphb200_ctx_create": (_i, [_i, _i, _i, _dp, _dp, _vpp]),
+    "sphb200_ctx_destroy": (None, [_vp]),
+    "sphb200_ctx_synchronize": (_i, [_vp]),
+    "sphb200_last_error": (_cp, [_vp]),
+    "sphb200_ctx_stream": (_vp, [_vp]),
+    "sphb200_ctx_launch_count": (_i64, [_vp]),
+    "sphb200_body_create": (_i, [_vp, _cp, _i64, _d, _d, _vpp]),
+    "sphb200_body_set_fluid": (_i, [_vp, _d, _d, _d]),
+    "sphb200_body_set_elastic": (_i, [_vp, _d, _d, _d]),
+    "sphb200_body_set_periodic": (_i, [_vp, _i, _d, _d]),
+    "sphb200_body_info": (_i, [_vp, _dp]),
+    "sphb200_var_register": (_i, [_vp, _cp, _i, _i, _vp]),
+    "sphb200_var_to_device": (_i, [_vp, _cp]),
+    "sphb200_var_to_host": (_i, [_vp, _cp]),
+    "sphb200_var_upload": (_i, [_vp, _cp, _vp]),
+    "sphb200_var_download": (_i, [_vp, _cp, _vp]),
+    "sphb200_var_device_ptr": (_i, [_vp, _cp, _vpp]),
+    "sphb200_ids_to_host": (_i, [_vp, _i64p, _i64p]),
+    "sphb200_cell_list_update": (_i, [_vp]),
+    "sphb200_cell_keys": (_i, [_vp, _i64p, _i64p]),
+    "sphb200_cell_offsets": (_i, [_vp, _i64p, _i64p]),
+    "sphb200_periodic_bounding": (_i, [_vp, _i]),
+    "sphb200_relation_inner_create": (_i, [_vp, _vpp]),
+    "sphb200_relation_contact_create": (_i, [_vp, _vpp, _i, _vpp]),
+    "sphb200_relation_update": (_i, [_vp]),
+    "sphb200_relation_neighbors": (_i, [_vp, _i, C.POINTER(C.c_int32), _i64p, _i64p]),
+    "sphb200_density_summation": (_i, [_vp, _vp, _i]),
+    "sphb200_integration_1st_half": (_i, [_vp, _vp, _i, _d]),
+    "sphb200_integration_2nd_half": (_i, [_vp, _vp, _i, _d]),
+    "sphb200_acoustic_dt": (_i, [_vp, _d, _dp]),
+    "sphb200_advection_dt": (_i, [_vp, _d, _d, _i, _dp]),
+    "sphb200_gravity_force": (_i, [_vp, _dp]),
+    "sphb200_viscous_force": (_i, [_vp]),
+    "sphb200_transport_velocity_correction": (_i, [_vp, _d]),
+    "sphb200_total_kinetic_energy": (_i, [_vp, _dp]),
+    "sphb200_total_mechanical_energy": (_i, [_vp, _dp, _dp]),
+    "sphb200_maximum_speed": (_i, [_vp, _dp]),
+    "sphb200_observe": (_i, [_vp, _cp, _i, _dp]),
+    "sphb200_correction_matrix": (_i, [_vp]),
+    "sphb200_solid_1st_half": (_i, [_vp, _i, _d]),
+    "sphb200_solid_2nd_half": (_i, [_vp, _d]),
+    "sphb200_solid_constrain": (_i, [_vp, _i64p, _i64]),
+    "sphb200_solid_dt": (_i, [_vp, _d, _dp]),
+    "sphb200_exclusive_scan_u32": (_i, [_vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), _i64, C.POINTER(C.c_uint64)]),
+    "sphb200_ctx_set_stream": (_i, [_vp, _vp]),
+    "sphb200_body_resize": (_i, [_vp, _i64]),
+    "sphb200_body_set_owned_pages": (_i, [_vp, _i, _i]),
+    "sphb200_body_owned_range": (_i, [_vp, _i64p, _i64p]),
+    "sphb200_ids_device_ptr": (_i, [_vp, _vpp, _vpp]),
+}
+
+
+def load():
+    """Load libsphb200.so (built by __graft_entry__.build()) and bind every declared symbol."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). There is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib

@@ -381,7 +381,7 @@ static sphb200_status cellListUpdate(sphb200_body *b)
     b->cell_list_valid = true;
     b->xV_vol_dirty = false;
     b->config_stamp++;
-    return SPHB200_OK;
+    return updateOwnedRange(b);
 }
 
 template <int D, class R>

@@ -251,7 +251,8 @@ void sphb200_ctx_destroy(sphb200_ctx *ctx)
         d->release();
     if (ctx->reduce_host)
         cudaFreeHost(ctx->reduce_host);
-    cudaStreamDestroy(ctx->stream);
+    if (ctx->owns_stream)
+        cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
 
@@ -278,6 +279,7 @@ sphb200_status sphb200_body_create(sphb200_ctx *ctx, const char *name, int64_t n
     b->ctx = ctx;
     b->name = name;
     b->n = n;
+    b->own_end = n;
     b->dp = dp;
     b->h_ratio = h_ratio;
     memset(b->params, 0, sizeof(b->params));

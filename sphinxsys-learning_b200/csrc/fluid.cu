@@ -93,13 +93,13 @@ __device__ __forceinline__ void loadXj(const typename Real4<R>::type *__restrict
 // ---------------------------------------------------------------------------------------------
 template <int D, class R>
 __global__ void __launch_bounds__(128)
-    k_density_summation(int64_t n, const typename Real4<R>::type *xV, ListP<R> in, ContactP<R> ct,
+    k_density_summation(int64_t i0, int64_t n, const typename Real4<R>::type *xV, ListP<R> in, ContactP<R> ct,
                         KernelP<R> kern, KernelP<R> kern_ct, PeriodicP<D, R> per, R rho0, R inv_sigma0,
                         const R *__restrict__ mass, R *__restrict__ rho_sum, R *__restrict__ rho, R *__restrict__ vol,
                         typename Real4<R>::type *xV_w, int free_surface)
 {
-    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
-    if (i >= n)
+    int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i < i0 || i >= n)
         return;
     const int lane = threadIdx.x & 31;
     R xi[D], Vi;
@@ -171,11 +171,11 @@ __global__ void __launch_bounds__(128)
 // ---------------------------------------------------------------------------------------------
 template <int D, class R>
 __global__ void __launch_bounds__(256)
-    k_first_half_init(int64_t n, R dt, R p0, R rho0, R *__restrict__ rho, const R *__restrict__ drho,
+    k_first_half_init(int64_t i0, int64_t n, R dt, R p0, R rho0, R *__restrict__ rho, const R *__restrict__ drho,
                       R *__restrict__ p, R *__restrict__ pos, const R *__restrict__ vel)
 {
-    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
-    if (i >= n)
+    int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i < i0 || i >= n)
         return;
     R r = rho[i] + drho[i] * dt * R(0.5);
     rho[i] = r;
@@ -187,16 +187,16 @@ __global__ void __launch_bounds__(256)
 
 template <int D, class R>
 __global__ void __launch_bounds__(128)
-    k_first_half(int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, ContactP<R> wall,
+    k_first_half(int64_t i0, int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, ContactP<R> wall,
                  KernelP<R> kern, KernelP<R> kern_w, PeriodicP<D, R> per, FluidP<R> fl, R dt,
                  const R *__restrict__ p, const R *__restrict__ rho, const R *__restrict__ mass,
                  const R *__restrict__ fprior, R *__restrict__ force, R *__restrict__ drho, R *__restrict__ vel,
                  unsigned long long *__restrict__ max_slot)
 {
-    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     const int lane = threadIdx.x & 31;
     R signal = R(0);
-    if (i < n)
+    if (i >= i0 && i < n)
     {
         R xi[D], Vi;
         loadXj<D, R>(xV, u32(i), xi, Vi);
@@ -299,13 +299,13 @@ __global__ void __launch_bounds__(128)
 // ---------------------------------------------------------------------------------------------
 template <int D, class R>
 __global__ void __launch_bounds__(128)
-    k_second_half(int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, ContactP<R> wall,
+    k_second_half(int64_t i0, int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, ContactP<R> wall,
                   KernelP<R> kern, KernelP<R> kern_w, PeriodicP<D, R> per, FluidP<R> fl, R dt,
                   const R *__restrict__ vel, R *__restrict__ pos, R *__restrict__ rho, R *__restrict__ drho,
                   R *__restrict__ force)
 {
-    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
-    if (i >= n)
+    int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i < i0 || i >= n)
         return;
     const int lane = threadIdx.x & 31;
     R xi[D], Vi, vi[D];
@@ -411,9 +411,9 @@ __global__ void __launch_bounds__(128)
 // ---------------------------------------------------------------------------------------------
 template <int D, class R>
 __global__ void __launch_bounds__(256)
-    k_acoustic_max(int64_t n, const R *__restrict__ vel, R c0, unsigned long long *__restrict__ slot)
+    k_acoustic_max(int64_t i0, int64_t n, const R *__restrict__ vel, R c0, unsigned long long *__restrict__ slot)
 {
-    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    int64_t i = i0 + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     R s = R(0);
     for (; i < n; i += int64_t(gridDim.x) * blockDim.x)
     {
@@ -430,10 +430,10 @@ __global__ void __launch_bounds__(256)
 
 template <int D, class R>
 __global__ void __launch_bounds__(256)
-    k_advection_max(int64_t n, const R *__restrict__ vel, const R *__restrict__ force, const R *__restrict__ fprior,
+    k_advection_max(int64_t i0, int64_t n, const R *__restrict__ vel, const R *__restrict__ force, const R *__restrict__ fprior,
                     const R *__restrict__ mass, R h, unsigned long long *__restrict__ slot)
 {
-    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    int64_t i = i0 + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     R s = R(0);
     for (; i < n; i += int64_t(gridDim.x) * blockDim.x)
     {
@@ -456,13 +456,13 @@ __global__ void __launch_bounds__(256)
 // kind 0: total kinetic energy, 1: total mechanical energy (general_reduce.cpp:54-79), 2: max |v|
 template <int D, class R>
 __global__ void __launch_bounds__(256)
-    k_observable(int64_t n, int kind, const R *__restrict__ vel, const R *__restrict__ mass, const R *__restrict__ pos,
+    k_observable(int64_t i0, int64_t n, int kind, const R *__restrict__ vel, const R *__restrict__ mass, const R *__restrict__ pos,
                  R gx, R gy, R gz, double *__restrict__ partial)
 {
     __shared__ double sh[8];
     const R g[3] = {gx, gy, gz};
     double s = 0.0;
-    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x)
+    for (int64_t i = i0 + blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x)
     {
         R v[D];
 #pragma unroll
@@ -515,11 +515,11 @@ __global__ void k_observable_final(int nb, int kind, const double *__restrict__ 
 // ---------------------------------------------------------------------------------------------
 template <int D, class R>
 __global__ void __launch_bounds__(256)
-    k_gravity(int64_t n, const R *__restrict__ mass, R gx, R gy, R gz, R *__restrict__ cur, R *__restrict__ prev,
+    k_gravity(int64_t i0, int64_t n, const R *__restrict__ mass, R gx, R gy, R gz, R *__restrict__ cur, R *__restrict__ prev,
               R *__restrict__ fprior)
 {
-    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
-    if (i >= n)
+    int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i < i0 || i >= n)
         return;
     const R g[3] = {gx, gy, gz};
 #pragma unroll
@@ -534,12 +534,12 @@ __global__ void __launch_bounds__(256)
 
 template <int D, class R>
 __global__ void __launch_bounds__(128)
-    k_viscous(int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, KernelP<R> kern,
+    k_viscous(int64_t i0, int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, KernelP<R> kern,
               PeriodicP<D, R> per, R mu, R h, const R *__restrict__ vel, R *__restrict__ vf, R *__restrict__ prev,
               R *__restrict__ fprior)
 {
-    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
-    if (i >= n)
+    int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i < i0 || i >= n)
         return;
     const int lane = threadIdx.x & 31;
     R xi[D], Vi, vi[D];
@@ -585,11 +585,11 @@ __global__ void __launch_bounds__(128)
 
 template <int D, class R>
 __global__ void __launch_bounds__(128)
-    k_transport_velocity(int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, KernelP<R> kern,
+    k_transport_velocity(int64_t i0, int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, KernelP<R> kern,
                          PeriodicP<D, R> per, R h2, R scaling, R *__restrict__ kgi, R *__restrict__ pos)
 {
-    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
-    if (i >= n)
+    int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i < i0 || i >= n)
         return;
     const int lane = threadIdx.x & 31;
     R xi[D], Vi;
@@ -630,11 +630,11 @@ __global__ void __launch_bounds__(128)
 // ObservingAQuantity: out[i] = Σ W_ij V_j q_j / (Σ W_ij V_j + tiny)
 template <int D, class R>
 __global__ void __launch_bounds__(128)
-    k_observe(int64_t n, const typename Real4<R>::type *__restrict__ xV_obs, ContactP<R> ct, KernelP<R> kern,
+    k_observe(int64_t i0, int64_t n, const typename Real4<R>::type *__restrict__ xV_obs, ContactP<R> ct, KernelP<R> kern,
               const R *q0, const R *q1, const R *q2, const R *q3, int width, double *__restrict__ out)
 {
-    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
-    if (i >= n)
+    int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i < i0 || i >= n)
         return;
     const int lane = threadIdx.x & 31;
     const R *qs[kMaxTargets] = {q0, q1, q2, q3};
@@ -754,7 +754,7 @@ static sphb200_status densitySummation(sphb200_relation *inner, sphb200_relation
     SPHB_TRY(checkRelation(inner, true, "density_summation"));
     if (contact)
         SPHB_TRY(checkRelation(contact, false, "density_summation"));
-    if (b->n == 0)
+    if (b->own_end <= b->own_begin)
         return SPHB200_OK;
     BodyP<D, R> &P = b->P<D, R>();
     SPHB_TRY((ensurePacked<D, R>(b)));
@@ -767,8 +767,8 @@ static sphb200_status densitySummation(sphb200_relation *inner, sphb200_relation
     SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
     SPHB_TRY(getVarPtr<R>(b, "VolumetricMeasure", 1, &vol, true));
     auto *xV = static_cast<typename Real4<R>::type *>(b->xV.p);
-    k_density_summation<D, R><<<gridFor(b->n, 128), 128, 0, ctx->stream>>>(
-        b->n, xV, listOf<R>(inner->lists[0]), ct, P.kern, kern_ct, P.per, R(b->rho0), R(1.0) / P.sigma0, mass, rho_sum,
+    k_density_summation<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
+        b->own_begin, b->own_end, xV, listOf<R>(inner->lists[0]), ct, P.kern, kern_ct, P.per, R(b->rho0), R(1.0) / P.sigma0, mass, rho_sum,
         rho, vol, xV, free_surface);
     SPHB_LAUNCH_CHECK(ctx);
     return SPHB200_OK;
@@ -782,7 +782,7 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
     SPHB_TRY(checkRelation(inner, true, "integration_1st_half"));
     if (wall)
         SPHB_TRY(checkRelation(wall, false, "integration_1st_half"));
-    if (b->n == 0)
+    if (b->own_end <= b->own_begin)
         return SPHB200_OK;
     BodyP<D, R> &P = b->P<D, R>();
     SPHB_TRY((ensurePacked<D, R>(b)));
@@ -800,11 +800,11 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
     SPHB_TRY(getVarPtr<R>(b, "Force", D, &force, true));
     SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
     const R dt = R(dt_);
-    k_first_half_init<D, R><<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(b->n, dt, fl.p0, fl.rho0, rho, drho, p, pos, vel);
+    k_first_half_init<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 256), 256, 0, ctx->stream>>>(b->own_begin, b->own_end, dt, fl.p0, fl.rho0, rho, drho, p, pos, vel);
     SPHB_LAUNCH_CHECK(ctx);
     SPHB_TRY(reduceReset(ctx, 0, false));
-    k_first_half<D, R><<<gridFor(b->n, 128), 128, 0, ctx->stream>>>(
-        b->n, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), wp, P.kern, kern_w,
+    k_first_half<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
+        b->own_begin, b->own_end, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), wp, P.kern, kern_w,
         P.per, fl, dt, p, rho, mass, fprior, force, drho, vel, static_cast<unsigned long long *>(ctx->reduce_dev.p));
     SPHB_LAUNCH_CHECK(ctx);
     for (auto *ob : ctx->bodies)
@@ -821,7 +821,7 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
     SPHB_TRY(checkRelation(inner, true, "integration_2nd_half"));
     if (wall)
         SPHB_TRY(checkRelation(wall, false, "integration_2nd_half"));
-    if (b->n == 0)
+    if (b->own_end <= b->own_begin)
         return SPHB200_OK;
     BodyP<D, R> &P = b->P<D, R>();
     SPHB_TRY((ensurePacked<D, R>(b)));
@@ -835,8 +835,8 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
     SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos, true));
     SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel, true));
     SPHB_TRY(getVarPtr<R>(b, "Force", D, &force, true));
-    k_second_half<D, R><<<gridFor(b->n, 128), 128, 0, ctx->stream>>>(
-        b->n, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), wp, P.kern, kern_w,
+    k_second_half<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
+        b->own_begin, b->own_end, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), wp, P.kern, kern_w,
         P.per, fl, R(dt_), vel, pos, rho, drho, force);
     SPHB_LAUNCH_CHECK(ctx);
     return SPHB200_OK;
@@ -852,9 +852,9 @@ static sphb200_status acousticDt(sphb200_body *b, double cfl, double *dt_out)
         R *vel;
         SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel, true));
         SPHB_TRY(reduceReset(ctx, 0, false));
-        if (b->n > 0)
+        if (b->own_end > b->own_begin)
         {
-            k_acoustic_max<D, R><<<148 * 4, 256, 0, ctx->stream>>>(b->n, vel, R(b->c0),
+            k_acoustic_max<D, R><<<148 * 4, 256, 0, ctx->stream>>>(b->own_begin, b->own_end, vel, R(b->c0),
                                                                   static_cast<unsigned long long *>(ctx->reduce_dev.p));
             SPHB_LAUNCH_CHECK(ctx);
         }
@@ -881,9 +881,9 @@ static sphb200_status advectionDt(sphb200_body *b, double U_ref, double cfl, int
     SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
     SPHB_TRY(getVarPtr<R>(b, "Mass", 1, &mass, true));
     SPHB_TRY(reduceReset(ctx, 1, false));
-    if (b->n > 0)
+    if (b->own_end > b->own_begin)
     {
-        k_advection_max<D, R><<<148 * 4, 256, 0, ctx->stream>>>(b->n, vel, force, fprior, mass, P.h,
+        k_advection_max<D, R><<<148 * 4, 256, 0, ctx->stream>>>(b->own_begin, b->own_end, vel, force, fprior, mass, P.h,
                                                                static_cast<unsigned long long *>(ctx->reduce_dev.p) + 1);
         SPHB_LAUNCH_CHECK(ctx);
     }
@@ -910,7 +910,7 @@ static sphb200_status observable(sphb200_body *b, int kind, const double *g, dou
     const int nb = 148 * 2;
     SPHB_CUDA(ctx, ctx->scratch_a.ensure(size_t(nb + 1) * 8));
     double *partial = static_cast<double *>(ctx->scratch_a.p);
-    k_observable<D, R><<<nb, 256, 0, ctx->stream>>>(b->n, kind, vel, mass, pos, g ? R(g[0]) : R(0), g ? R(g[1]) : R(0),
+    k_observable<D, R><<<nb, 256, 0, ctx->stream>>>(b->own_begin, b->own_end, kind, vel, mass, pos, g ? R(g[0]) : R(0), g ? R(g[1]) : R(0),
                                                     (g && D == 3) ? R(g[2]) : R(0), partial);
     SPHB_LAUNCH_CHECK(ctx);
     k_observable_final<<<1, 32, 0, ctx->stream>>>(nb, kind, partial, partial + nb);
@@ -925,14 +925,14 @@ template <int D, class R>
 static sphb200_status gravityForce(sphb200_body *b, const double *g)
 {
     sphb200_ctx *ctx = b->ctx;
-    if (b->n == 0)
+    if (b->own_end <= b->own_begin)
         return SPHB200_OK;
     R *mass, *cur, *prev, *fprior;
     SPHB_TRY(getVarPtr<R>(b, "Mass", 1, &mass, true));
     SPHB_TRY(getVarPtr<R>(b, "GravityForce", D, &cur));
     SPHB_TRY(getVarPtr<R>(b, "PreviousGravityForce", D, &prev, true));
     SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
-    k_gravity<D, R><<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(b->n, mass, R(g[0]), R(g[1]), D == 3 ? R(g[2]) : R(0),
+    k_gravity<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 256), 256, 0, ctx->stream>>>(b->own_begin, b->own_end, mass, R(g[0]), R(g[1]), D == 3 ? R(g[2]) : R(0),
                                                                cur, prev, fprior);
     SPHB_LAUNCH_CHECK(ctx);
     return SPHB200_OK;
@@ -944,7 +944,7 @@ static sphb200_status viscousForce(sphb200_relation *inner)
     sphb200_ctx *ctx = inner->ctx;
     sphb200_body *b = inner->body;
     SPHB_TRY(checkRelation(inner, true, "viscous_force"));
-    if (b->n == 0)
+    if (b->own_end <= b->own_begin)
         return SPHB200_OK;
     BodyP<D, R> &P = b->P<D, R>();
     SPHB_TRY((ensurePacked<D, R>(b)));
@@ -953,8 +953,8 @@ static sphb200_status viscousForce(sphb200_relation *inner)
     SPHB_TRY(getVarPtr<R>(b, "ViscousForce", D, &vf));
     SPHB_TRY(getVarPtr<R>(b, "PreviousViscousForce", D, &prev, true));
     SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
-    k_viscous<D, R><<<gridFor(b->n, 128), 128, 0, ctx->stream>>>(
-        b->n, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), P.kern, P.per,
+    k_viscous<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
+        b->own_begin, b->own_end, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), P.kern, P.per,
         R(b->mu), P.h, vel, vf, prev, fprior);
     SPHB_LAUNCH_CHECK(ctx);
     return SPHB200_OK;
@@ -966,7 +966,7 @@ static sphb200_status transportVelocity(sphb200_relation *inner, double coeffici
     sphb200_ctx *ctx = inner->ctx;
     sphb200_body *b = inner->body;
     SPHB_TRY(checkRelation(inner, true, "transport_velocity_correction"));
-    if (b->n == 0)
+    if (b->own_end <= b->own_begin)
         return SPHB200_OK;
     BodyP<D, R> &P = b->P<D, R>();
     SPHB_TRY((ensurePacked<D, R>(b)));
@@ -974,8 +974,8 @@ static sphb200_status transportVelocity(sphb200_relation *inner, double coeffici
     SPHB_TRY(getVarPtr<R>(b, "KernelGradientIntegral", D, &kgi));
     SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos, true));
     R h2 = P.h * P.h;
-    k_transport_velocity<D, R><<<gridFor(b->n, 128), 128, 0, ctx->stream>>>(
-        b->n, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), P.kern, P.per, h2,
+    k_transport_velocity<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
+        b->own_begin, b->own_end, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), P.kern, P.per, h2,
         R(coefficient) * h2, kgi, pos);
     SPHB_LAUNCH_CHECK(ctx);
     return SPHB200_OK;
@@ -987,7 +987,7 @@ static sphb200_status observe(sphb200_relation *contact, const char *name, int w
     sphb200_ctx *ctx = contact->ctx;
     sphb200_body *b = contact->body;
     SPHB_TRY(checkRelation(contact, false, "observe"));
-    if (b->n == 0)
+    if (b->own_end <= b->own_begin)
         return SPHB200_OK;
     SPHB_TRY((ensurePacked<D, R>(b)));
     ContactP<R> ct;
@@ -1005,8 +1005,8 @@ static sphb200_status observe(sphb200_relation *contact, const char *name, int w
     }
     SPHB_CUDA(ctx, ctx->scratch_a.ensure(size_t(b->n) * size_t(width) * 8));
     double *dev_out = static_cast<double *>(ctx->scratch_a.p);
-    k_observe<D, R><<<gridFor(b->n, 128), 128, 0, ctx->stream>>>(
-        b->n, static_cast<const typename Real4<R>::type *>(b->xV.p), ct, kern, q[0], q[1], q[2], q[3], width, dev_out);
+    k_observe<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
+        b->own_begin, b->own_end, static_cast<const typename Real4<R>::type *>(b->xV.p), ct, kern, q[0], q[1], q[2], q[3], width, dev_out);
     SPHB_LAUNCH_CHECK(ctx);
     SPHB_CUDA(ctx, cudaMemcpyAsync(out, dev_out, size_t(b->n) * size_t(width) * 8, cudaMemcpyDeviceToHost, ctx->stream));
     SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

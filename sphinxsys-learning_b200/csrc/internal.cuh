@@ -160,6 +160,7 @@ struct sphb200_ctx
     int device = 0, ndim = 3, real_bytes = 8;
     double sys_lo[3] = {0, 0, 0}, sys_hi[3] = {0, 0, 0};
     cudaStream_t stream = nullptr;
+    bool owns_stream = true;
     std::string error;
     int64_t launches = 0;
     std::vector<sphb200_body *> bodies;
@@ -196,6 +197,10 @@ struct sphb200_body
     bool xV_vol_dirty = true; // Vol component of xV must be refreshed before the next interaction
     uint64_t config_stamp = 0;
     bool acoustic_max_valid = false; // reduce slot 0 holds max(c0+|v|) from the last 1st half
+    // slab decomposition: particles [own_begin, own_end) (cell-sorted order) are owned by this rank,
+    // the rest are halo copies that only serve as neighbours j.  Defaults to the whole body.
+    int64_t own_begin = 0, own_end = 0;
+    int page_lo = -1, page_hi = -1; // owned range of cell pages along axis 0 (x slowest), or -1
 
     template <int D, class R>
     sphb::BodyP<D, R> &P() { return *reinterpret_cast<sphb::BodyP<D, R> *>(params); }
@@ -273,6 +278,9 @@ sphb200_status exclusiveScanU32(sphb200_ctx *ctx, const u32 *in, u32 *out, int64
 // refresh the Vol component of xV (and nothing else) if a dynamics changed VolumetricMeasure
 template <int D, class R>
 sphb200_status ensurePacked(sphb200_body *b);
+
+// slab.cu: owned pages → owned particle range, after a cell_list_update
+sphb200_status updateOwnedRange(sphb200_body *b);
 
 // reduction slots (device u64 bit patterns of non-negative doubles)
 sphb200_status reduceReset(sphb200_ctx *ctx, int slot, bool for_min);

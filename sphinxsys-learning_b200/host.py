@@ -1,0 +1,298 @@
+"""Host-side mirror (Python) of the reference's interface for the hot path, over the C ABI.
+
+The production host binding is the C++ adapter in include/sphb200_adapter.hpp (the reference is C++);
+this module is the same surface for the test-suite and bench harness.  Method names follow the
+reference's operators so the parity tests read like the reference's own mains:
+
+  SPHSystem            sphinxsys_system/sph_system.h:50-154
+  Body                 bodies/base_body.h:62-201 + particles/base_particles.h:80-263 (named variables)
+  InnerRelation / ContactRelation        body_relations/*.h  (updateConfiguration)
+  density_summation / integration_1st_half / ...   particle_dynamics/fluid_dynamics/* exec(dt)
+
+Every call goes to libsphb200.so; nothing is computed in Python.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+
+
+def _np_real(real_bytes):
+    return np.float64 if real_bytes == 8 else np.float32
+
+
+class SPHSystem:
+    """One context per GPU. `lo`/`hi` are the user's system_domain_bounds; like the reference's ctor
+    (sph_system.cpp:39) they are expanded by 4*dp_ref."""
+
+    backend = "sphb200"
+
+    def __init__(self, ndim, lo, hi, dp_ref, real_bytes=8, device=0, expand=True, stream=None):
+        self.lib = capi.load()
+        self.ndim, self.real_bytes, self.dtype = int(ndim), int(real_bytes), _np_real(real_bytes)
+        ex = 4.0 * dp_ref if expand else 0.0
+        self.lo = np.asarray(lo, dtype=np.float64) - ex
+        self.hi = np.asarray(hi, dtype=np.float64) + ex
+        lo3 = (C.c_double * 3)(*list(self.lo) + [0.0] * (3 - ndim))
+        hi3 = (C.c_double * 3)(*list(self.hi) + [0.0] * (3 - ndim))
+        h = C.c_void_p()
+        st = self.lib.sphb200_ctx_create(device, ndim, real_bytes, lo3, hi3, C.byref(h))
+        if st != capi.OK:
+            why = {capi.ERR_NO_DEVICE: "no CUDA device (there is no CPU fallback)",
+                   capi.ERR_INVALID: "invalid arguments", capi.ERR_CUDA: "CUDA error"}.get(st, "?")
+            raise capi.SphB200Error(st, f"ctx_create failed: {why}")
+        self.h = h
+        self.bodies, self.relations = [], []
+        if stream is not None:
+            self.check(self.lib.sphb200_ctx_set_stream(self.h, C.c_void_p(int(stream))))
+
+    def check(self, st):
+        if st != capi.OK:
+            raise capi.SphB200Error(st, self.lib.sphb200_last_error(self.h).decode())
+
+    def close(self):
+        if self.h:
+            self.lib.sphb200_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def synchronize(self):
+        self.check(self.lib.sphb200_ctx_synchronize(self.h))
+
+    @property
+    def stream(self):
+        return self.lib.sphb200_ctx_stream(self.h)
+
+    @property
+    def launches(self):
+        return int(self.lib.sphb200_ctx_launch_count(self.h))
+
+    def add_body(self, name, n, dp, h_ratio=1.3):
+        b = Body(self, name, n, dp, h_ratio)
+        self.bodies.append(b)
+        return b
+
+    def inner(self, body):
+        r = Relation(self, body, None)
+        self.relations.append(r)
+        return r
+
+    def contact(self, body, targets):
+        r = Relation(self, body, list(targets))
+        self.relations.append(r)
+        return r
+
+    def exclusive_scan(self, values):
+        v = np.ascontiguousarray(values, dtype=np.uint32)
+        out = np.zeros_like(v)
+        total = C.c_uint64()
+        self.check(self.lib.sphb200_exclusive_scan_u32(
+            self.h, v.ctypes.data_as(C.POINTER(C.c_uint32)), out.ctypes.data_as(C.POINTER(C.c_uint32)),
+            v.size, C.byref(total)))
+        return out, int(total.value)
+
+    # ---- dynamics (exec) ---------------------------------------------------------------------
+    def density_summation(self, inner, contact=None, free_surface=False):
+        self.check(self.lib.sphb200_density_summation(inner.h, contact.h if contact else None, int(free_surface)))
+
+    def integration_1st_half(self, inner, wall=None, riemann=True, dt=0.0):
+        self.check(self.lib.sphb200_integration_1st_half(inner.h, wall.h if wall else None, int(riemann), dt))
+
+    def integration_2nd_half(self, inner, wall=None, riemann=True, dt=0.0):
+        self.check(self.lib.sphb200_integration_2nd_half(inner.h, wall.h if wall else None, int(riemann), dt))
+
+    def acoustic_dt(self, body, cfl=0.6):
+        out = C.c_double()
+        self.check(self.lib.sphb200_acoustic_dt(body.h, cfl, C.byref(out)))
+        return out.value
+
+    def advection_dt(self, body, U_ref, cfl=0.25, viscous=False):
+        out = C.c_double()
+        self.check(self.lib.sphb200_advection_dt(body.h, U_ref, cfl, int(viscous), C.byref(out)))
+        return out.value
+
+    def gravity_force(self, body, g):
+        g3 = (C.c_double * 3)(*list(g) + [0.0] * (3 - len(g)))
+        self.check(self.lib.sphb200_gravity_force(body.h, g3))
+
+    def viscous_force(self, inner):
+        self.check(self.lib.sphb200_viscous_force(inner.h))
+
+    def transport_velocity_correction(self, inner, coefficient=0.2):
+        self.check(self.lib.sphb200_transport_velocity_correction(inner.h, coefficient))
+
+    def total_kinetic_energy(self, body):
+        out = C.c_double()
+        self.check(self.lib.sphb200_total_kinetic_energy(body.h, C.byref(out)))
+        return out.value
+
+    def total_mechanical_energy(self, body, g):
+        g3 = (C.c_double * 3)(*list(g) + [0.0] * (3 - len(g)))
+        out = C.c_double()
+        self.check(self.lib.sphb200_total_mechanical_energy(body.h, g3, C.byref(out)))
+        return out.value
+
+    def maximum_speed(self, body):
+        out = C.c_double()
+        self.check(self.lib.sphb200_maximum_speed(body.h, C.byref(out)))
+        return out.value
+
+    def observe(self, contact, name, width=1):
+        out = np.zeros(contact.body.n * width, dtype=np.float64)
+        self.check(self.lib.sphb200_observe(contact.h, name.encode(), width, out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out.reshape(contact.body.n, width) if width > 1 else out
+
+    def correction_matrix(self, inner):
+        self.check(self.lib.sphb200_correction_matrix(inner.h))
+
+    def solid_1st_half(self, inner, decomposed, dt):
+        self.check(self.lib.sphb200_solid_1st_half(inner.h, int(decomposed), dt))
+
+    def solid_2nd_half(self, inner, dt):
+        self.check(self.lib.sphb200_solid_2nd_half(inner.h, dt))
+
+    def solid_constrain(self, body, original_ids):
+        ids = np.ascontiguousarray(original_ids, dtype=np.int64)
+        self.check(self.lib.sphb200_solid_constrain(body.h, ids.ctypes.data_as(C.POINTER(C.c_int64)), ids.size))
+
+    def solid_dt(self, body, cfl=0.6):
+        out = C.c_double()
+        self.check(self.lib.sphb200_solid_dt(body.h, cfl, C.byref(out)))
+        return out.value
+
+
+class Body:
+    def __init__(self, system, name, n, dp, h_ratio):
+        self.sys, self.lib, self.name = system, system.lib, name
+        self.n, self.dp, self.h_ratio = int(n), float(dp), float(h_ratio)
+        h = C.c_void_p()
+        system.check(self.lib.sphb200_body_create(system.h, name.encode(), self.n, dp, h_ratio, C.byref(h)))
+        self.h = h
+        self.widths = {"Position": system.ndim, "VolumetricMeasure": 1}
+
+    def set_fluid(self, rho0, c0, mu=0.0):
+        self.sys.check(self.lib.sphb200_body_set_fluid(self.h, rho0, c0, mu))
+
+    def set_elastic(self, rho0, youngs, poisson):
+        self.sys.check(self.lib.sphb200_body_set_elastic(self.h, rho0, youngs, poisson))
+
+    def set_periodic(self, axis, lo, hi):
+        self.sys.check(self.lib.sphb200_body_set_periodic(self.h, axis, lo, hi))
+
+    def info(self):
+        out = (C.c_double * 12)()
+        self.sys.check(self.lib.sphb200_body_info(self.h, out))
+        o = list(out)
+        d = self.sys.ndim
+        return {"h": o[0], "rc": o[1], "W0": o[2], "sigma0": o[3], "mesh_lo": o[4:4 + d], "spacing": o[7],
+                "cells": [int(c) for c in o[8:8 + d]], "n": int(o[11])}
+
+    def register(self, name, width=1, evolving=True):
+        self.sys.check(self.lib.sphb200_var_register(self.h, name.encode(), width, int(evolving), None))
+        self.widths[name] = width
+
+    def set(self, name, values, evolving=True):
+        """register (if new) + upload; values shaped (n,) or (n, width) in the CURRENT particle order"""
+        a = np.ascontiguousarray(values, dtype=self.sys.dtype)
+        width = 1 if a.ndim == 1 else a.shape[1]
+        assert a.shape[0] == self.n, (name, a.shape, self.n)
+        self.register(name, width, evolving)
+        if self.n:
+            self.sys.check(self.lib.sphb200_var_upload(self.h, name.encode(), a.ctypes.data_as(C.c_void_p)))
+
+    def get(self, name, width=None):
+        width = width or self.widths.get(name, 1)
+        out = np.zeros((self.n, width) if width > 1 else (self.n,), dtype=self.sys.dtype)
+        if self.n:
+            self.sys.check(self.lib.sphb200_var_download(self.h, name.encode(), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def device_ptr(self, name):
+        p = C.c_void_p()
+        self.sys.check(self.lib.sphb200_var_device_ptr(self.h, name.encode(), C.byref(p)))
+        return p.value
+
+    def ids(self):
+        o = np.zeros(self.n, dtype=np.int64)
+        s = np.zeros(self.n, dtype=np.int64)
+        self.sys.check(self.lib.sphb200_ids_to_host(self.h, o.ctypes.data_as(C.POINTER(C.c_int64)),
+                                                     s.ctypes.data_as(C.POINTER(C.c_int64))))
+        return o, s
+
+    def update_cell_list(self):
+        self.sys.check(self.lib.sphb200_cell_list_update(self.h))
+
+    def sort(self):
+        """ParticleSorting::exec - the cell list update already keeps the body cell-sorted"""
+        self.update_cell_list()
+
+    def cell_keys(self):
+        lin = np.zeros(self.n, dtype=np.int64)
+        mor = np.zeros(self.n, dtype=np.int64)
+        self.sys.check(self.lib.sphb200_cell_keys(self.h, lin.ctypes.data_as(C.POINTER(C.c_int64)),
+                                                   mor.ctypes.data_as(C.POINTER(C.c_int64))))
+        return lin, mor
+
+    def cell_offsets(self):
+        nc = C.c_int64()
+        self.sys.check(self.lib.sphb200_cell_offsets(self.h, None, C.byref(nc)))
+        out = np.zeros(nc.value + 1, dtype=np.int64)
+        self.sys.check(self.lib.sphb200_cell_offsets(self.h, out.ctypes.data_as(C.POINTER(C.c_int64)), C.byref(nc)))
+        return out
+
+    def periodic_bounding(self, axis):
+        self.sys.check(self.lib.sphb200_periodic_bounding(self.h, axis))
+
+    def periodic_cell_list(self, axis):
+        """PeriodicConditionUsingCellLinkedList::update_cell_linked_list_: the ghost images are
+        generated on the fly by the neighbour search, nothing to insert."""
+
+    def resize(self, n_new):
+        self.sys.check(self.lib.sphb200_body_resize(self.h, int(n_new)))
+        self.n = int(n_new)
+
+    def set_owned_pages(self, lo, hi):
+        self.sys.check(self.lib.sphb200_body_set_owned_pages(self.h, int(lo), int(hi)))
+
+    def owned_range(self):
+        b, e = C.c_int64(), C.c_int64()
+        self.sys.check(self.lib.sphb200_body_owned_range(self.h, C.byref(b), C.byref(e)))
+        return b.value, e.value
+
+    def ids_device_ptr(self):
+        a, b = C.c_void_p(), C.c_void_p()
+        self.sys.check(self.lib.sphb200_ids_device_ptr(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+
+class Relation:
+    def __init__(self, system, body, targets):
+        self.sys, self.lib, self.body, self.targets = system, system.lib, body, targets
+        h = C.c_void_p()
+        if targets is None:
+            system.check(self.lib.sphb200_relation_inner_create(body.h, C.byref(h)))
+        else:
+            arr = (C.c_void_p * len(targets))(*[t.h for t in targets])
+            system.check(self.lib.sphb200_relation_contact_create(body.h, arr, len(targets), C.byref(h)))
+        self.h = h
+
+    def update(self):
+        """SPHRelation::updateConfiguration"""
+        self.sys.check(self.lib.sphb200_relation_update(self.h))
+
+    def neighbors(self, k=0):
+        """(counts[n], flat j in list order) of target k - parity/debug"""
+        n = self.body.n
+        total = C.c_int64()
+        self.sys.check(self.lib.sphb200_relation_neighbors(self.h, k, None, None, C.byref(total)))
+        counts = np.zeros(n, dtype=np.int32)
+        j = np.zeros(total.value, dtype=np.int64)
+        self.sys.check(self.lib.sphb200_relation_neighbors(
+            self.h, k, counts.ctypes.data_as(C.POINTER(C.c_int32)), j.ctypes.data_as(C.POINTER(C.c_int64)), C.byref(total)))
+        return counts, j

@@ -1,0 +1,76 @@
+"""CPU-side tests (no GPU): the C-ABI library loads and exports every declared symbol, the oracle
+reproduces the reference's closed-form known answers and stays inside the reference's own regression
+envelopes (tests/golden, extracted from the reference's regression_test_tool XML files)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol(pk):
+    header = open(os.path.join(ROOT, "include", "sphb200.h")).read()
+    declared = set(re.findall(r"\b(sphb200_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 45
+    lib = ctypes.CDLL(pk.capi.LIB_PATH)
+    missing = [s for s in sorted(declared) if not hasattr(lib, s)]
+    assert not missing, missing
+    assert declared == set(pk.capi.SIGNATURES), declared ^ set(pk.capi.SIGNATURES)
+
+
+def test_no_device_is_a_loud_error(pk):
+    """the product path must not fall back to the CPU"""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(pk.capi.SphB200Error) as e:
+        pk.host.SPHSystem(3, [0, 0, 0], [1, 1, 1], 0.1)
+    assert e.value.status == pk.capi.ERR_NO_DEVICE
+
+
+def test_product_package_never_touches_the_oracle():
+    pkg = os.path.join(ROOT, "sphinxsys-learning_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "liboracle" not in src and "import oracle" not in src and "from oracle" not in src, f
+
+
+def test_lattice_sizes_and_kernel_kats(pk, oracle):
+    """N_f = 3200 (2-D dp 0.025), 8000 (3-D dp 0.05); sigma0 / W0 closed forms"""
+    c2 = pk.cases.DamBreak(oracle, ndim=2, dp=0.025)
+    assert c2.water.n == 3200 and c2.water.info()["cells"] == [93, 93]
+    i2 = c2.water.info()
+    assert abs(i2["sigma0"] - 1616.7570433713395) < 1e-9 and abs(i2["W0"] - 527.377326221665) < 1e-9
+    c3 = pk.cases.DamBreak(oracle, ndim=3, dp=0.05)
+    assert c3.water.n == 8000 and c3.water.info()["cells"] == [52, 26, 14]
+    i3 = c3.water.info()
+    assert abs(i3["sigma0"] - 8076.006270278393) < 1e-8 and abs(i3["W0"] - 1521.2807487163413) < 1e-9
+    counts, _ = c3.inner.neighbors()
+    assert counts.max() == 80
+    counts, _ = c2.inner.neighbors()
+    assert counts.max() == 20
+    # golden sample 0 of the reference: total mechanical energy of the initial 2-D column is exactly 1
+    assert abs(c2.mechanical_energy() - 1.0000000000000016) < 1e-13
+    # contact search depth formula of the reference (base_body_relation.cpp:10-16)
+    assert oracle.load().orc_search_depth(c3.sys.h, c3.wall_contact.id, 0) in (1, 2)
+    tc = pk.cases.TwistingColumn(oracle, dp=0.1)
+    assert tc.column.n == 6100
+    tg = pk.cases.TaylorGreen(oracle, dp=0.01)
+    assert tg.water.n == 10000
+    assert abs(tg.sys.total_kinetic_energy(tg.water) - 0.25) < 1e-12  # golden sample 0 = 0.25000000000000011
+
+
+def test_oracle_inside_reference_regression_envelopes():
+    """run-level pin of the oracle: same observables the reference's regression tests store"""
+    from oracle import validate_golden as vg
+    r = vg.dambreak_2d(3)
+    assert r["max_rel_dev"] < 0.01, r          # north-star run-level criterion: 1 %
+    r = vg.taylor_green(2)
+    assert r["max_rel_dev"] < 0.01, r
+    r = vg.twisting_column(60)
+    assert r["max_rel_dev"] < 0.01, r

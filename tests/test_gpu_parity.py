@@ -1,0 +1,290 @@
+"""GPU parity tests: libsphb200.so (through the C ABI) against the CPU oracle on identical inputs.
+
+Bars (BASELINE.json north_star): cell/sort indices and neighbour sets bit-exact; per-step density,
+pressure and velocity fields within rel-L2 1e-6 (fp64) / 1e-4 (fp32); max-type reductions bit-exact.
+The cross-policy equality pattern follows the reference's device tests
+(tests/tests_sycl/unit_test_src/shared/particle_dynamics/test_particle_reduce_sycl/test_particle_reduce.cpp:13-70).
+"""
+import numpy as np
+import pytest
+
+from helpers import FP_TOL, field, jitter, pair_set, rel_l2, seeded_state, set_field
+
+pytestmark = pytest.mark.gpu
+
+
+def both(pk, gpu, oracle, cls, **kw):
+    return cls(gpu, **kw), cls(oracle, **kw)
+
+
+# ------------------------------------------------------------------------------------------------
+# primitives
+# ------------------------------------------------------------------------------------------------
+def test_exclusive_scan_reference_kat(pk, gpu):
+    """tests/unit_tests_src/shared/particle_dynamics/configuration_dynamics/test_exclusive_scan/test_exclusive_scan.cpp:8-25"""
+    s = gpu.SPHSystem(3, [0, 0, 0], [1, 1, 1], 0.1)
+    out, total = s.exclusive_scan([3, 2, 3, 5, 0, 1, 3, 2, 5, 1, 0])
+    assert out.tolist() == [0, 3, 5, 8, 13, 13, 14, 17, 19, 24, 25][:11]
+    assert total == 25
+
+
+@pytest.mark.parametrize("n", [0, 1, 31, 4096, 4097, 1_000_003, 9_000_001])
+def test_exclusive_scan_sizes(pk, gpu, n):
+    s = gpu.SPHSystem(3, [0, 0, 0], [1, 1, 1], 0.1)
+    rng = np.random.default_rng(n)
+    v = rng.integers(0, 50, size=n, dtype=np.uint32)
+    out, total = s.exclusive_scan(v)
+    ref = np.concatenate([[0], np.cumsum(v, dtype=np.uint64)])
+    assert total == int(ref[-1])
+    assert np.array_equal(out.astype(np.uint64), ref[:-1])
+
+
+# ------------------------------------------------------------------------------------------------
+# cell list + sort
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("ndim,dp,real_bytes", [(2, 0.025, 8), (3, 0.05, 8), (3, 0.05, 4), (2, 0.025, 4)])
+def test_cell_keys_sort_and_ids(pk, gpu, oracle, ndim, dp, real_bytes):
+    g, o = both(pk, gpu, oracle, pk.cases.DamBreak, ndim=ndim, dp=dp, real_bytes=real_bytes)
+    for body_g, body_o in ((g.water, o.water), (g.wall, o.wall)):
+        jitter(body_g, 0.3)
+        jitter(body_o, 0.3)
+        pos_in = field(body_g, "Position")
+        body_g.update_cell_list()
+        body_o.update_cell_list()
+        lin_g, mor_g = body_g.cell_keys()
+        lin_o, mor_o = body_o.cell_keys()
+        oid, sid = body_g.ids()
+        oid_o, _ = body_o.ids()
+        # keys per particle (by original id) are bit-identical to the reference algorithm's
+        a = np.empty_like(lin_g)
+        a[oid] = lin_g
+        b = np.empty_like(lin_o)
+        b[oid_o] = lin_o
+        assert np.array_equal(a, b)
+        a[oid] = mor_g
+        b[oid_o] = mor_o
+        assert np.array_equal(a, b)
+        # the body is cell-sorted, stably
+        assert np.all(np.diff(lin_g) >= 0)
+        same = np.diff(lin_g) == 0
+        assert np.all(np.diff(oid)[same] > 0)
+        # ids are a consistent permutation pair and payload moved with the particles, bit for bit
+        assert np.array_equal(np.sort(oid), np.arange(body_g.n))
+        assert np.array_equal(sid[oid], np.arange(body_g.n))
+        assert np.array_equal(field(body_g, "Position"), pos_in)
+        # CSR offsets agree with the keys
+        off = body_g.cell_offsets()
+        counts = np.bincount(lin_g, minlength=len(off) - 1)
+        assert np.array_equal(np.diff(off), counts)
+        assert body_g.info()["cells"] == body_o.info()["cells"]
+        assert body_g.info()["sigma0"] == body_o.info()["sigma0"]
+
+
+def test_particles_outside_mesh_are_clamped(pk, gpu, oracle):
+    """base_mesh.hxx:9-15 clamps the cell index to [0, cells-1]"""
+    def make(backend):
+        s = backend.SPHSystem(3, [0, 0, 0], [1, 1, 1], 0.1)
+        b = s.add_body("b", 4, 0.1)
+        b.set("Position", np.array([[-5.0, 0.5, 0.5], [0.5, 9.0, 0.5], [0.5, 0.5, -3.0], [0.51, 0.52, 0.53]]))
+        b.set("VolumetricMeasure", np.full(4, 1e-3))
+        b.update_cell_list()
+        lin, mor = b.cell_keys()
+        oid, _ = b.ids()
+        out = np.empty_like(lin)
+        out[oid] = lin
+        return out
+    assert np.array_equal(make(gpu), make(oracle))
+
+
+# ------------------------------------------------------------------------------------------------
+# neighbour sets
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("ndim,dp,real_bytes,amp", [(2, 0.025, 8, 0.0), (2, 0.025, 8, 0.3), (3, 0.05, 8, 0.0),
+                                                    (3, 0.05, 8, 0.3), (3, 0.05, 4, 0.3), (2, 0.025, 4, 0.3)])
+def test_neighbor_sets_inner_and_contact(pk, gpu, oracle, ndim, dp, real_bytes, amp):
+    g, o = both(pk, gpu, oracle, pk.cases.DamBreak, ndim=ndim, dp=dp, real_bytes=real_bytes)
+    for c in (g, o):
+        if amp:
+            jitter(c.water, amp)
+            c.water.update_cell_list()
+            c.update_configuration()
+    pg, po = pair_set(g.inner), pair_set(o.inner)
+    assert pg.shape == po.shape and np.array_equal(pg, po)
+    pg, po = pair_set(g.wall_contact, 0, g.wall), pair_set(o.wall_contact, 0, o.wall)
+    assert pg.shape == po.shape and np.array_equal(pg, po)
+    pg, po = pair_set(g.obs_contact, 0, g.water), pair_set(o.obs_contact, 0, o.water)
+    assert pg.shape == po.shape and np.array_equal(pg, po)
+    if amp == 0.0 and real_bytes == 8:
+        counts, _ = g.inner.neighbors()
+        assert counts.max() == (20 if ndim == 2 else 80)  # interior lattice KAT, SURVEY §8c
+
+
+def test_neighbor_sets_periodic(pk, gpu, oracle):
+    g, o = both(pk, gpu, oracle, pk.cases.TaylorGreen, dp=0.02)
+    pg, po = pair_set(g.inner), pair_set(o.inner)
+    assert np.array_equal(pg, po)
+    counts, _ = g.inner.neighbors()
+    assert counts.min() == 20 and counts.max() == 20  # fully periodic lattice: everybody is interior
+    for c in (g, o):
+        jitter(c.water, 0.45)
+        c.water.periodic_bounding(0)
+        c.water.periodic_bounding(1)
+        c.configure()
+    assert np.array_equal(field(g.water, "Position"), field(o.water, "Position"))
+    pg, po = pair_set(g.inner), pair_set(o.inner)
+    assert pg.shape == po.shape and np.array_equal(pg, po)
+
+
+# ------------------------------------------------------------------------------------------------
+# per-step fields
+# ------------------------------------------------------------------------------------------------
+FLUID_FIELDS = ["Density", "Pressure", "Velocity", "Position", "Force", "DensityChangeRate"]
+
+
+def load_state(case, state):
+    for name, v in state.items():
+        set_field(case.water, name, v)
+
+
+@pytest.mark.parametrize("ndim,dp,real_bytes", [(2, 0.025, 8), (3, 0.05, 8), (3, 0.05, 4), (2, 0.025, 4)])
+def test_fluid_dynamics_single_calls(pk, gpu, oracle, ndim, dp, real_bytes):
+    tol = FP_TOL[real_bytes]
+    g, o = both(pk, gpu, oracle, pk.cases.DamBreak, ndim=ndim, dp=dp, real_bytes=real_bytes)
+    for c in (g, o):
+        jitter(c.water, 0.2)
+        c.water.update_cell_list()
+        c.update_configuration()
+    state = seeded_state(g)
+    for c in (g, o):
+        load_state(c, state)
+    # time-step reductions: max is order independent -> bit-exact
+    assert g.sys.acoustic_dt(g.water) == o.sys.acoustic_dt(o.water)
+    assert g.sys.advection_dt(g.water, g.U_ref) == o.sys.advection_dt(o.water, o.U_ref)
+    # density summation (free surface + wall)
+    for c in (g, o):
+        c.sys.density_summation(c.inner, c.wall_contact, free_surface=True)
+    assert rel_l2(field(g.water, "DensitySummation"), field(o.water, "DensitySummation")) < tol
+    assert rel_l2(field(g.water, "Density"), field(o.water, "Density")) < tol
+    dt = 0.3 * g.sys.acoustic_dt(g.water)
+    for c in (g, o):
+        load_state(c, state)
+        c.sys.integration_1st_half(c.inner, c.wall_contact, True, dt)
+    for name in FLUID_FIELDS:
+        assert rel_l2(field(g.water, name), field(o.water, name)) < tol, name
+    # the 1st half leaves max(c0+|v|) on the device: the fused reduction must equal a fresh one
+    dt_fused = g.sys.acoustic_dt(g.water)
+    set_field(g.water, "Velocity", field(g.water, "Velocity"))  # invalidates the fused value
+    assert dt_fused == g.sys.acoustic_dt(g.water)
+    for c in (g, o):
+        c.sys.integration_2nd_half(c.inner, c.wall_contact, True, dt)
+    for name in FLUID_FIELDS:
+        assert rel_l2(field(g.water, name), field(o.water, name)) < tol, name
+    # inner-only, no Riemann dissipation (Taylor-Green flavour)
+    for c in (g, o):
+        load_state(c, state)
+        c.sys.integration_1st_half(c.inner, None, False, dt)
+        c.sys.integration_2nd_half(c.inner, None, False, dt)
+    for name in FLUID_FIELDS:
+        assert rel_l2(field(g.water, name), field(o.water, name)) < tol, name
+    # observables and probes
+    e_g, e_o = g.mechanical_energy(), o.mechanical_energy()
+    assert abs(e_g - e_o) <= tol * abs(e_o)
+    assert abs(g.sys.maximum_speed(g.water) - o.sys.maximum_speed(o.water)) <= 1e-12 * o.sys.maximum_speed(o.water)
+    pg, po = g.probe_pressure(), o.probe_pressure()
+    assert np.allclose(pg, po, rtol=tol, atol=tol)
+
+
+@pytest.mark.parametrize("ndim,dp,steps", [(2, 0.025, 30), (3, 0.05, 12)])
+def test_dambreak_steps_match_oracle(pk, gpu, oracle, ndim, dp, steps):
+    """whole advection steps (density summation, acoustic loop, sort, cell list, relations) in lockstep"""
+    g, o = both(pk, gpu, oracle, pk.cases.DamBreak, ndim=ndim, dp=dp, real_bytes=8)
+    for s in range(steps):
+        rg = g.advection_step(sort_interval=5)
+        ro = o.advection_step(sort_interval=5)
+        assert rg[1] == ro[1]
+        assert abs(rg[0] - ro[0]) <= 1e-12 * ro[0]
+    for name in ("Density", "Pressure", "Velocity", "Position"):
+        assert rel_l2(field(g.water, name), field(o.water, name)) < 1e-6, name
+    assert abs(g.mechanical_energy() - o.mechanical_energy()) < 1e-9
+    assert g.n_acoustic == o.n_acoustic
+
+
+def test_taylor_green_steps_match_oracle(pk, gpu, oracle):
+    g, o = both(pk, gpu, oracle, pk.cases.TaylorGreen, dp=0.02)
+    for s in range(10):
+        rg, ro = g.advection_step(), o.advection_step()
+        assert rg[1] == ro[1]
+    for name in ("Density", "Pressure", "Velocity", "Position", "ViscousForce", "KernelGradientIntegral"):
+        assert rel_l2(field(g.water, name), field(o.water, name)) < 1e-6, name
+    ke_g, ke_o = g.sys.total_kinetic_energy(g.water), o.sys.total_kinetic_energy(o.water)
+    assert abs(ke_g - ke_o) < 1e-9 * ke_o
+
+
+@pytest.mark.parametrize("decomposed", [True, False])
+def test_twisting_column_steps_match_oracle(pk, gpu, oracle, decomposed):
+    g, o = both(pk, gpu, oracle, pk.cases.TwistingColumn, dp=0.1, decomposed=decomposed)
+    assert rel_l2(field(g.column, "LinearGradientCorrectionMatrix"), field(o.column, "LinearGradientCorrectionMatrix")) < 1e-9
+    for s in range(40):
+        dg, do = g.step(), o.step()
+        assert abs(dg - do) <= 1e-9 * do
+    for name in ("Position", "Velocity", "DeformationGradient", "Density", "Force"):
+        assert rel_l2(field(g.column, name), field(o.column, name)) < 1e-6, name
+    pg, vg = g.observed()
+    po, vo = o.observed()
+    assert np.allclose(pg, po, rtol=1e-8, atol=1e-10) and np.allclose(vg, vo, rtol=1e-6, atol=1e-8)
+
+
+# ------------------------------------------------------------------------------------------------
+# error behaviour and edge cases
+# ------------------------------------------------------------------------------------------------
+def test_errors_and_empty_bodies(pk, gpu):
+    s = gpu.SPHSystem(3, [0, 0, 0], [1, 1, 1], 0.1)
+    empty = s.add_body("empty", 0, 0.1)
+    empty.update_cell_list()
+    inner = s.inner(empty)
+    inner.update()
+    s.density_summation(inner, None, True)
+    s.integration_1st_half(inner, None, True, 1e-3)
+    s.integration_2nd_half(inner, None, True, 1e-3)
+    one = s.add_body("one", 1, 0.1)
+    one.set("Position", np.array([[0.5, 0.5, 0.5]]))
+    one.set("VolumetricMeasure", np.array([1e-3]))
+    one.set("Mass", np.array([1e-3]))
+    r = s.inner(one)
+    with pytest.raises(pk.capi.SphB200Error):  # relation before any cell list
+        r.update()
+    one.update_cell_list()
+    r.update()
+    counts, j = r.neighbors()
+    assert counts.tolist() == [0] and j.size == 0
+    s.density_summation(r, None, False)
+    assert np.isclose(one.get("DensitySummation")[0], one.info()["W0"] / one.info()["sigma0"])
+    one.update_cell_list()
+    with pytest.raises(pk.capi.SphB200Error):  # stale relation after a re-sort
+        s.density_summation(r, None, False)
+    with pytest.raises(pk.capi.SphB200Error):  # unknown variable
+        one.get("NoSuchVariable")
+
+
+def test_large_lattice_properties(pk, gpu):
+    """size-independent properties at ~1.1 M fluid particles (the oracle does not run at this size in seconds)"""
+    c = pk.cases.DamBreak(gpu, ndim=3, dp=1.0 / 104.0, real_bytes=8, with_observer=False)
+    w = c.water
+    assert w.n == 208 * 104 * 52
+    lin, _ = w.cell_keys()
+    assert np.all(np.diff(lin) >= 0)
+    counts, j = c.inner.neighbors()
+    assert counts.max() == 80
+    assert counts.sum() % 2 == 0
+    # symmetry of the inner relation: (i, j) present iff (j, i) present
+    i = np.repeat(np.arange(w.n, dtype=np.int64), counts)
+    key_ij = np.sort(i * w.n + j)
+    key_ji = np.sort(j * w.n + i)
+    assert np.array_equal(key_ij, key_ji)
+    c.sys.density_summation(c.inner, c.wall_contact, True)
+    rho = w.get("DensitySummation")
+    interior = counts == 80
+    assert np.allclose(rho[interior], 1.0, rtol=0, atol=1e-12)
+    for _ in range(2):
+        c.advection_step()
+    assert np.isfinite(c.mechanical_energy())
