@@ -80,6 +80,9 @@ sphb200_status sphb200_var_upload(sphb200_body *b, const char *name, const void 
 sphb200_status sphb200_var_download(sphb200_body *b, const char *name, void *dst);
 /* DelegatedData(par_device): raw device pointer, valid until the next cell_list_update of b */
 sphb200_status sphb200_var_device_ptr(sphb200_body *b, const char *name, void **out);
+/* Reals per particle of a registered variable (DiscreteVariable<T>: sizeof(T)/sizeof(Real),
+ * sphinxsys_variable.h:196-236); dynamics register their own outputs (e.g. "ViscousForce") on first use */
+sphb200_status sphb200_var_width(sphb200_body *b, const char *name, int *width);
 /* OriginalID / SortedID (particles/base_particles.cpp:33-38), widened to int64 */
 sphb200_status sphb200_ids_to_host(sphb200_body *b, int64_t *original_id, int64_t *sorted_id);
 

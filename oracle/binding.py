@@ -31,7 +31,7 @@ def load():
         "orc_create": (vp, [i, i, dp, dp]), "orc_destroy": (None, [vp]),
         "orc_body_add": (i, [vp, cp, l, d, d]), "orc_body_material": (None, [vp, i, d, d, d]),
         "orc_body_elastic": (None, [vp, i, d, d, d]), "orc_body_periodic": (None, [vp, i, i, d, d]),
-        "orc_var": (vp, [vp, i, cp, i, i]), "orc_body_info": (None, [vp, i, dp]),
+        "orc_var": (vp, [vp, i, cp, i, i]), "orc_var_width": (i, [vp, i, cp]), "orc_body_info": (None, [vp, i, dp]),
         "orc_ids": (None, [vp, i, lp, lp]), "orc_cell_keys": (None, [vp, i, lp, lp]),
         "orc_update_cell_list": (None, [vp, i]), "orc_periodic_bounding": (None, [vp, i, i]),
         "orc_periodic_cell_list": (None, [vp, i, i]), "orc_sort": (None, [vp, i]),
@@ -202,7 +202,7 @@ class Body:
             self._view(name, width, evolving)
 
     def get(self, name, width=None):
-        width = width or self.widths.get(name, 1)
+        width = self.lib.orc_var_width(self.sys.h, self.id, name.encode()) or width or self.widths.get(name, 1)
         return self._view(name, width).copy() if self.n else np.zeros((0, width) if width > 1 else (0,), self.sys.dtype)
 
     def ids(self):

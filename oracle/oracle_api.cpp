@@ -148,6 +148,15 @@ void *orc_var(void *sys, int body, const char *name, int width, int evolving)
     });
     return p;
 }
+int orc_var_width(void *sys, int body, const char *name)
+{
+    int w = 0;
+    DISPATCH(sys, {
+        auto it = S.bodies[body]->vars.find(name);
+        w = it == S.bodies[body]->vars.end() ? 0 : it->second.width;
+    });
+    return w;
+}
 void orc_body_info(void *sys, int body, double *out /* h, rc, W0, sigma0, lo[3], spacing, cells[3] */)
 {
     DISPATCH(sys, {

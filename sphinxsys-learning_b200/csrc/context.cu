@@ -454,6 +454,17 @@ sphb200_status sphb200_var_device_ptr(sphb200_body *b, const char *name, void **
     return SPHB200_OK;
 }
 
+sphb200_status sphb200_var_width(sphb200_body *b, const char *name, int *width)
+{
+    if (!b || !name || !width)
+        return SPHB200_ERR_INVALID;
+    Var *v = b->find(name);
+    if (!v)
+        return b->ctx->fail(SPHB200_ERR_NOT_FOUND, std::string("variable '") + name + "' is not registered");
+    *width = v->width;
+    return SPHB200_OK;
+}
+
 sphb200_status sphb200_ids_to_host(sphb200_body *b, int64_t *original_id, int64_t *sorted_id)
 {
     if (!b)

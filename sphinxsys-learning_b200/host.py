@@ -206,8 +206,13 @@ class Body:
         if self.n:
             self.sys.check(self.lib.sphb200_var_upload(self.h, name.encode(), a.ctypes.data_as(C.c_void_p)))
 
+    def width(self, name):
+        w = C.c_int()
+        self.sys.check(self.lib.sphb200_var_width(self.h, name.encode(), C.byref(w)))
+        return w.value
+
     def get(self, name, width=None):
-        width = width or self.widths.get(name, 1)
+        width = self.width(name)  # the library is authoritative (dynamics register their own outputs)
         out = np.zeros((self.n, width) if width > 1 else (self.n,), dtype=self.sys.dtype)
         if self.n:
             self.sys.check(self.lib.sphb200_var_download(self.h, name.encode(), out.ctypes.data_as(C.c_void_p)))
