@@ -314,6 +314,7 @@ sphb200_status ensurePacked(sphb200_body *b)
         pos, vol, static_cast<typename Real4<R>::type *>(b->xV.p), b->n, 1);
     SPHB_LAUNCH_CHECK(ctx);
     b->xV_vol_dirty = false;
+    b->rec_b_valid = false;
     return SPHB200_OK;
 }
 template sphb200_status ensurePacked<2, float>(sphb200_body *);
@@ -380,6 +381,7 @@ static sphb200_status cellListUpdate(sphb200_body *b)
     }
     b->cell_list_valid = true;
     b->xV_vol_dirty = false;
+    b->rec_b_valid = false;
     b->config_stamp++;
     return updateOwnedRange(b);
 }

@@ -243,7 +243,7 @@ void sphb200_ctx_destroy(sphb200_ctx *ctx)
         for (auto &kv : b->vars)
             kv.second->dev.release();
         for (DevBuf *d : {&b->original_id, &b->sorted_id, &b->cell_of, &b->rank_in_cell, &b->perm, &b->cell_count,
-                          &b->cell_offset, &b->xV, &b->tmp_var})
+                          &b->cell_offset, &b->xV, &b->tmp_var, &b->rec_a, &b->rec_b})
             d->release();
         delete b;
     }
@@ -386,6 +386,8 @@ static void touched(sphb200_body *b, const char *name)
         b->xV_vol_dirty = true;
     if (!strcmp(name, "Velocity"))
         b->acoustic_max_valid = false;
+    if (!strcmp(name, "Velocity") || !strcmp(name, "VolumetricMeasure") || !strcmp(name, "Pressure"))
+        b->rec_b_valid = false;
     if (!strcmp(name, "Position"))
         b->cell_list_valid = b->cell_list_valid; // the frozen snapshot stays; a new cell_list_update refreshes it
 }

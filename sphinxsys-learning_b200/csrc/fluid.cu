@@ -167,40 +167,98 @@ __global__ void __launch_bounds__(128)
 }
 
 // ---------------------------------------------------------------------------------------------
-// Integration1stHalf: K1 initialization, K2 interaction (+wall) + update + max(c0+|v|)
+// Acoustic sub-step.  Neighbour state is gathered from packed records (internal.cuh Rec8):
+//   K1 k_first_half_init : rho, p, x update; writes rec_a[i] = {x_cfg, Vol | p_new, v}
+//   K2 k_first_half      : gathers rec_a[j] (x_cfg, Vol, p); writes rec_b[i] = {x_cfg, Vol | p, v_new}
+//   K3 k_second_half     : gathers rec_b[j] (x_cfg, Vol, v)
+// rec_a / rec_b ping-pong so that no kernel reads a line another thread of the same launch writes.
 // ---------------------------------------------------------------------------------------------
 template <int D, class R>
+__device__ __forceinline__ void recSplit(const R *rec, R *x, R &V, R &p, R *v)
+{
+    x[0] = rec[0];
+    x[1] = rec[1];
+    if (D == 3)
+        x[D - 1] = rec[2];
+    V = rec[3];
+    p = rec[4];
+    v[0] = rec[5];
+    v[1] = rec[6];
+    if (D == 3)
+        v[D - 1] = rec[7];
+}
+template <int D, class R>
+__device__ __forceinline__ void recJoin(R *rec, const R *x, R V, R p, const R *v)
+{
+    rec[0] = x[0];
+    rec[1] = x[1];
+    rec[2] = D == 3 ? x[D - 1] : R(0);
+    rec[3] = V;
+    rec[4] = p;
+    rec[5] = v[0];
+    rec[6] = v[1];
+    rec[7] = D == 3 ? v[D - 1] : R(0);
+}
+
+// rec[i] = {xV[i] | p[i], vel[i]} from the named variables (after a re-sort or a host-side write)
+template <int D, class R>
 __global__ void __launch_bounds__(256)
-    k_first_half_init(int64_t i0, int64_t n, R dt, R p0, R rho0, R *__restrict__ rho, const R *__restrict__ drho,
-                      R *__restrict__ p, R *__restrict__ pos, const R *__restrict__ vel)
+    k_pack_rec(int64_t n, const typename Real4<R>::type *__restrict__ xV, const R *__restrict__ p, const R *__restrict__ vel,
+               Rec8<R> *__restrict__ rec)
+{
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    R x[D], V, v[D], r8[8];
+    loadXj<D, R>(xV, u32(i), x, V);
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        v[a] = vel[i * D + a];
+    recJoin<D, R>(r8, x, V, p[i], v);
+    stRec(rec, i, r8);
+}
+
+template <int D, class R>
+__global__ void __launch_bounds__(256)
+    k_first_half_init(int64_t i0, int64_t n, R dt, R p0, R rho0, const typename Real4<R>::type *__restrict__ xV,
+                      R *__restrict__ rho, const R *__restrict__ drho, R *__restrict__ p, R *__restrict__ pos,
+                      const R *__restrict__ vel, Rec8<R> *__restrict__ rec_a)
 {
     int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (i < i0 || i >= n)
         return;
     R r = rho[i] + drho[i] * dt * R(0.5);
     rho[i] = r;
-    p[i] = p0 * (r / rho0 - R(1.0));
+    R pn = p0 * (r / rho0 - R(1.0));
+    p[i] = pn;
+    R x[D], V, v[D], r8[8];
+    loadXj<D, R>(xV, u32(i), x, V);
 #pragma unroll
     for (int d = 0; d < D; ++d)
-        pos[i * D + d] += vel[i * D + d] * dt * R(0.5);
+    {
+        v[d] = vel[i * D + d];
+        pos[i * D + d] += v[d] * dt * R(0.5);
+    }
+    recJoin<D, R>(r8, x, V, pn, v);
+    stRec(rec_a, i, r8);
 }
 
-template <int D, class R>
+template <int D, class R, bool PER>
 __global__ void __launch_bounds__(128)
-    k_first_half(int64_t i0, int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, ContactP<R> wall,
-                 KernelP<R> kern, KernelP<R> kern_w, PeriodicP<D, R> per, FluidP<R> fl, R dt,
-                 const R *__restrict__ p, const R *__restrict__ rho, const R *__restrict__ mass,
-                 const R *__restrict__ fprior, R *__restrict__ force, R *__restrict__ drho, R *__restrict__ vel,
-                 unsigned long long *__restrict__ max_slot)
+    k_first_half(int64_t i0, int64_t n, const Rec8<R> *__restrict__ rec_a, Rec8<R> *__restrict__ rec_b, ListP<R> in,
+                 ContactP<R> wall, KernelP<R> kern, KernelP<R> kern_w, PeriodicP<D, R> per, FluidP<R> fl, R dt,
+                 const R *__restrict__ rho, const R *__restrict__ mass, const R *__restrict__ fprior, R *__restrict__ force,
+                 R *__restrict__ drho, R *__restrict__ vel, unsigned long long *__restrict__ max_slot)
 {
     int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     const int lane = threadIdx.x & 31;
     R signal = R(0);
     if (i >= i0 && i < n)
     {
-        R xi[D], Vi;
-        loadXj<D, R>(xV, u32(i), xi, Vi);
-        const R pi = p[i], rhoi = rho[i], mi = mass[i];
+        R ri[8], xi[D], Vi, pi, vi[D];
+        ldRec(rec_a, u32(i), ri);
+        recSplit<D, R>(ri, xi, Vi, pi, vi);
+        const R rhoi = rho[i], mi = mass[i];
         R f[D];
 #pragma unroll
         for (int a = 0; a < D; ++a)
@@ -213,10 +271,15 @@ __global__ void __launch_bounds__(128)
             for (u32 k = 0; k < cnt; ++k)
             {
                 u32 j = __ldg(lst + size_t(k) * 32u);
-                R xj[D], Vj;
-                loadXj<D, R>(xV, j, xj, Vj);
-                R pj = __ldg(p + j);
-                periodicImage<D, R>(xi, xj, per);
+                R rj[8], xj[D];
+                ldRecXVp(rec_a, j, rj);
+                xj[0] = rj[0];
+                xj[1] = rj[1];
+                if (D == 3)
+                    xj[D - 1] = rj[2];
+                const R Vj = rj[3], pj = rj[4];
+                if (PER)
+                    periodicImage<D, R>(xi, xj, per);
                 Pair<D, R> g;
                 pairGeometry<D, R>(xi, xj, kern, g);
                 R dWV = g.dW * Vj;
@@ -284,9 +347,11 @@ __global__ void __launch_bounds__(128)
         for (int a = 0; a < D; ++a)
         {
             force[i * D + a] = fo[a];
-            v[a] = vel[i * D + a] + (fp[a] + fo[a]) / mi * dt; // fluid_integration.hpp:58-61
+            v[a] = vi[a] + (fp[a] + fo[a]) / mi * dt; // fluid_integration.hpp:58-61
             vel[i * D + a] = v[a];
         }
+        recJoin<D, R>(ri, xi, Vi, pi, v);
+        stRec(rec_b, i, ri);
         signal = fl.c0 + sqrt_r(sqnormExact<D, R>(v)); // fluid_time_step.cpp:21-24
     }
     signal = warpMax<R>(signal);
@@ -297,25 +362,22 @@ __global__ void __launch_bounds__(128)
 // ---------------------------------------------------------------------------------------------
 // Integration2ndHalf: initialization + interaction (+wall) + update in one kernel
 // ---------------------------------------------------------------------------------------------
-template <int D, class R>
+template <int D, class R, bool PER>
 __global__ void __launch_bounds__(128)
-    k_second_half(int64_t i0, int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, ContactP<R> wall,
-                  KernelP<R> kern, KernelP<R> kern_w, PeriodicP<D, R> per, FluidP<R> fl, R dt,
-                  const R *__restrict__ vel, R *__restrict__ pos, R *__restrict__ rho, R *__restrict__ drho,
-                  R *__restrict__ force)
+    k_second_half(int64_t i0, int64_t n, const Rec8<R> *__restrict__ rec_b, ListP<R> in, ContactP<R> wall, KernelP<R> kern,
+                  KernelP<R> kern_w, PeriodicP<D, R> per, FluidP<R> fl, R dt, R *__restrict__ pos, R *__restrict__ rho,
+                  R *__restrict__ drho, R *__restrict__ force)
 {
     int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (i < i0 || i >= n)
         return;
     const int lane = threadIdx.x & 31;
-    R xi[D], Vi, vi[D];
-    loadXj<D, R>(xV, u32(i), xi, Vi);
+    R ri[8], xi[D], Vi, pi_unused, vi[D];
+    ldRec(rec_b, u32(i), ri);
+    recSplit<D, R>(ri, xi, Vi, pi_unused, vi);
 #pragma unroll
     for (int a = 0; a < D; ++a)
-    {
-        vi[a] = vel[i * D + a];
         pos[i * D + a] += vi[a] * dt * R(0.5); // fluid_integration.hpp:167-170
-    }
     R rate = R(0);
     R pd[D];
 #pragma unroll
@@ -328,10 +390,11 @@ __global__ void __launch_bounds__(128)
         for (u32 k = 0; k < cnt; ++k)
         {
             u32 j = __ldg(lst + size_t(k) * 32u);
-            R xj[D], Vj, vj[D];
-            loadXj<D, R>(xV, j, xj, Vj);
-            loadVec<D, R>(vel, j, vj);
-            periodicImage<D, R>(xi, xj, per);
+            R rj[8], xj[D], vj[D], Vj, pj_unused;
+            ldRec(rec_b, j, rj);
+            recSplit<D, R>(rj, xj, Vj, pj_unused, vj);
+            if (PER)
+                periodicImage<D, R>(xi, xj, per);
             Pair<D, R> g;
             pairGeometry<D, R>(xi, xj, kern, g);
             R dWV = g.dW * Vj;
@@ -771,6 +834,17 @@ static sphb200_status densitySummation(sphb200_relation *inner, sphb200_relation
         b->own_begin, b->own_end, xV, listOf<R>(inner->lists[0]), ct, P.kern, kern_ct, P.per, R(b->rho0), R(1.0) / P.sigma0, mass, rho_sum,
         rho, vol, xV, free_surface);
     SPHB_LAUNCH_CHECK(ctx);
+    if (!free_surface)
+        b->rec_b_valid = false; // Vol changed
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status ensureRecBuffers(sphb200_body *b)
+{
+    size_t need = size_t(b->n > 0 ? b->n : 1) * sizeof(Rec8<R>);
+    SPHB_CUDA(b->ctx, b->rec_a.ensure(need));
+    SPHB_CUDA(b->ctx, b->rec_b.ensure(need));
     return SPHB200_OK;
 }
 
@@ -786,6 +860,7 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
         return SPHB200_OK;
     BodyP<D, R> &P = b->P<D, R>();
     SPHB_TRY((ensurePacked<D, R>(b)));
+    SPHB_TRY((ensureRecBuffers<D, R>(b)));
     ContactP<R> wp;
     KernelP<R> kern_w = P.kern;
     SPHB_TRY((makeContactP<D, R>(wall, 4, wp, kern_w)));
@@ -800,16 +875,35 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
     SPHB_TRY(getVarPtr<R>(b, "Force", D, &force, true));
     SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
     const R dt = R(dt_);
-    k_first_half_init<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 256), 256, 0, ctx->stream>>>(b->own_begin, b->own_end, dt, fl.p0, fl.rho0, rho, drho, p, pos, vel);
+    auto *xV = static_cast<const typename Real4<R>::type *>(b->xV.p);
+    auto *rec_a = static_cast<Rec8<R> *>(b->rec_a.p);
+    auto *rec_b = static_cast<Rec8<R> *>(b->rec_b.p);
+    const int64_t span = b->own_end - (b->own_begin & ~int64_t(31));
+    if (b->own_begin > 0 || b->own_end < b->n)
+    {
+        // slab run: the halo copies (not visited as i) still serve as neighbours j
+        k_pack_rec<D, R><<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(b->n, xV, p, vel, rec_a);
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    k_first_half_init<D, R><<<gridFor(span, 256), 256, 0, ctx->stream>>>(b->own_begin, b->own_end, dt, fl.p0, fl.rho0, xV, rho, drho, p,
+                                                                       pos, vel, rec_a);
     SPHB_LAUNCH_CHECK(ctx);
     SPHB_TRY(reduceReset(ctx, 0, false));
-    k_first_half<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
-        b->own_begin, b->own_end, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), wp, P.kern, kern_w,
-        P.per, fl, dt, p, rho, mass, fprior, force, drho, vel, static_cast<unsigned long long *>(ctx->reduce_dev.p));
+    auto *slot = static_cast<unsigned long long *>(ctx->reduce_dev.p);
+    if (P.per.mask)
+        k_first_half<D, R, true><<<gridFor(span, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_a, rec_b, listOf<R>(inner->lists[0]),
+                                                                            wp, P.kern, kern_w, P.per, fl, dt, rho, mass, fprior,
+                                                                            force, drho, vel, slot);
+    else
+        k_first_half<D, R, false><<<gridFor(span, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_a, rec_b, listOf<R>(inner->lists[0]),
+                                                                             wp, P.kern, kern_w, P.per, fl, dt, rho, mass, fprior,
+                                                                             force, drho, vel, slot);
     SPHB_LAUNCH_CHECK(ctx);
     for (auto *ob : ctx->bodies)
         ob->acoustic_max_valid = false;
     b->acoustic_max_valid = true;
+    // rec_b now holds {x_cfg, Vol | p, v_new} of every owned particle
+    b->rec_b_valid = (b->own_begin == 0 && b->own_end == b->n);
     return SPHB200_OK;
 }
 
@@ -825,19 +919,33 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
         return SPHB200_OK;
     BodyP<D, R> &P = b->P<D, R>();
     SPHB_TRY((ensurePacked<D, R>(b)));
+    SPHB_TRY((ensureRecBuffers<D, R>(b)));
     ContactP<R> wp;
     KernelP<R> kern_w = P.kern;
     SPHB_TRY((makeContactP<D, R>(wall, 2 | 8, wp, kern_w)));
     FluidP<R> fl = makeFluidP<R>(b, P.h, riemann != 0);
-    R *rho, *drho, *pos, *vel, *force;
+    R *rho, *drho, *pos, *vel, *force, *p;
     SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
     SPHB_TRY(getVarPtr<R>(b, "DensityChangeRate", 1, &drho, true));
     SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos, true));
     SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel, true));
     SPHB_TRY(getVarPtr<R>(b, "Force", D, &force, true));
-    k_second_half<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
-        b->own_begin, b->own_end, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), wp, P.kern, kern_w,
-        P.per, fl, R(dt_), vel, pos, rho, drho, force);
+    SPHB_TRY(getVarPtr<R>(b, "Pressure", 1, &p, true));
+    auto *rec_b = static_cast<Rec8<R> *>(b->rec_b.p);
+    if (!b->rec_b_valid)
+    {
+        k_pack_rec<D, R><<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(b->n, static_cast<const typename Real4<R>::type *>(b->xV.p), p, vel,
+                                                                    rec_b);
+        SPHB_LAUNCH_CHECK(ctx);
+        b->rec_b_valid = (b->own_begin == 0 && b->own_end == b->n);
+    }
+    const int64_t span = b->own_end - (b->own_begin & ~int64_t(31));
+    if (P.per.mask)
+        k_second_half<D, R, true><<<gridFor(span, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_b, listOf<R>(inner->lists[0]), wp,
+                                                                             P.kern, kern_w, P.per, fl, R(dt_), pos, rho, drho, force);
+    else
+        k_second_half<D, R, false><<<gridFor(span, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_b, listOf<R>(inner->lists[0]), wp,
+                                                                              P.kern, kern_w, P.per, fl, R(dt_), pos, rho, drho, force);
     SPHB_LAUNCH_CHECK(ctx);
     return SPHB200_OK;
 }

@@ -40,6 +40,15 @@ struct Real4<double>
     typedef double4 type;
 };
 
+// Packed per-particle record of the acoustic sub-step kernels: one aligned 8-Real line
+// {x, y, z, Vol | p, vx, vy, vz} (32 B in fp32 = one L2 sector, 64 B in fp64 = two), fetched per
+// neighbour with 256-bit loads.  x and Vol are the values frozen at configuration time.
+template <class R>
+struct alignas(8 * sizeof(R)) Rec8
+{
+    R a[8];
+};
+
 // ---------------------------------------------------------------------------------------------
 // Device-side parameter blocks (passed by value to kernels)
 // ---------------------------------------------------------------------------------------------
@@ -191,6 +200,8 @@ struct sphb200_body
     sphb::DevBuf cell_of, rank_in_cell, perm;        // u32[n]
     sphb::DevBuf cell_count, cell_offset;            // u32[cells+1]
     sphb::DevBuf xV;                                 // Real4[n]: frozen position + Vol
+    sphb::DevBuf rec_a, rec_b;                       // Rec8[n]: {xV | p, v} before / after the 1st-half update
+    bool rec_b_valid = false;                        // rec_b matches xV, Pressure and Velocity
     sphb::DevBuf tmp_var;                            // permutation double buffer
     int64_t n_cells = 0;
     bool cell_list_valid = false;
@@ -317,6 +328,48 @@ __device__ __forceinline__ double4 ldg4(const double4 *p)
     const double2 *q = reinterpret_cast<const double2 *>(p);
     double2 a = __ldg(q), b = __ldg(q + 1);
     return make_double4(a.x, a.y, b.x, b.y);
+}
+
+// 256-bit loads/stores of record halves (LDG.E.256 on sm_100a)
+__device__ __forceinline__ void ld256(const float *p, float *v)
+{
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "l"(p));
+}
+__device__ __forceinline__ void ld256(const double *p, double *v)
+{
+    asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3]) : "l"(p));
+}
+__device__ __forceinline__ void st256(float *p, const float *v)
+{
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]),
+                 "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
+                 : "memory");
+}
+__device__ __forceinline__ void st256(double *p, const double *v)
+{
+    asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(v[0]), "d"(v[1]), "d"(v[2]), "d"(v[3]) : "memory");
+}
+// whole record (fp32: one 256-bit access, fp64: two)
+__device__ __forceinline__ void ldRec(const Rec8<float> *r, u32 j, float *v) { ld256(r[j].a, v); }
+__device__ __forceinline__ void ldRec(const Rec8<double> *r, u32 j, double *v)
+{
+    ld256(r[j].a, v);
+    ld256(r[j].a + 4, v + 4);
+}
+// {x, y, z, Vol, p}: fp32 gets the whole line anyway, fp64 adds one 8-byte load from the second sector
+__device__ __forceinline__ void ldRecXVp(const Rec8<float> *r, u32 j, float *v) { ld256(r[j].a, v); }
+__device__ __forceinline__ void ldRecXVp(const Rec8<double> *r, u32 j, double *v)
+{
+    ld256(r[j].a, v);
+    v[4] = __ldg(r[j].a + 4);
+}
+__device__ __forceinline__ void stRec(Rec8<float> *r, int64_t i, const float *v) { st256(r[i].a, v); }
+__device__ __forceinline__ void stRec(Rec8<double> *r, int64_t i, const double *v)
+{
+    st256(r[i].a, v);
+    st256(r[i].a + 4, v + 4);
 }
 
 template <class R>

@@ -271,7 +271,10 @@ static sphb200_status relationUpdate(sphb200_relation *r)
             sp.depth++;
         L.total_entries = L.total_pairs = 0;
         if (n == 0)
+        {
+            r->target_stamp[k] = tgt->config_stamp;
             continue;
+        }
         auto *xs = static_cast<const typename Real4<R>::type *>(src->xV.p);
         auto *xt = static_cast<const typename Real4<R>::type *>(tgt->xV.p);
         const u32 *off = static_cast<const u32 *>(tgt->cell_offset.p);

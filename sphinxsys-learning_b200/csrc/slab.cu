@@ -102,6 +102,7 @@ sphb200_status sphb200_body_resize(sphb200_body *b, int64_t n_new)
     b->own_end = n_new;
     b->cell_list_valid = false;
     b->xV_vol_dirty = true;
+    b->rec_b_valid = false;
     b->acoustic_max_valid = false;
     b->config_stamp++;
     return SPHB200_OK;
