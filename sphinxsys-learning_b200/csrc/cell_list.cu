@@ -362,11 +362,11 @@ static sphb200_status cellListUpdate(sphb200_body *b)
         for (auto &kv : b->vars)
         {
             Var &v = *kv.second;
-            SPHB_CUDA(ctx, b->tmp_var.ensure(v.dev.bytes));
+            SPHB_CUDA(ctx, v.alt.ensure(size_t(n) * size_t(v.width) * sizeof(R)));
             k_permute<R><<<gridFor(n * v.width, 256), 256, 0, st>>>(static_cast<const R *>(v.dev.p),
-                                                                    static_cast<R *>(b->tmp_var.p), perm, n, v.width);
+                                                                    static_cast<R *>(v.alt.p), perm, n, v.width);
             SPHB_LAUNCH_CHECK(ctx);
-            std::swap(v.dev, b->tmp_var);
+            std::swap(v.dev, v.alt);
         }
         u32 *oid_tmp = static_cast<u32 *>(ctx->scratch_a.p), *cell_tmp = static_cast<u32 *>(ctx->scratch_b.p);
         k_permute_ids<<<gridFor(n, 256), 256, 0, st>>>(static_cast<const u32 *>(b->original_id.p), oid_tmp,

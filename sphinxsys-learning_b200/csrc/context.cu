@@ -241,7 +241,10 @@ void sphb200_ctx_destroy(sphb200_ctx *ctx)
     for (auto *b : ctx->bodies)
     {
         for (auto &kv : b->vars)
+        {
             kv.second->dev.release();
+            kv.second->alt.release();
+        }
         for (DevBuf *d : {&b->original_id, &b->sorted_id, &b->cell_of, &b->rank_in_cell, &b->perm, &b->cell_count,
                           &b->cell_offset, &b->xV, &b->tmp_var, &b->rec_a, &b->rec_b})
             d->release();

@@ -20,6 +20,24 @@
 
 using namespace sphb;
 
+// occupancy / ILP knobs of the two pair-sum kernels of the acoustic sub-step (resident 128-thread
+// blocks per SM the register allocation must allow, and the neighbour-loop unroll depth)
+#ifndef SPHB_MINB_F64
+#define SPHB_MINB_F64 8
+#endif
+#ifndef SPHB_MINB_F32
+#define SPHB_MINB_F32 8
+#endif
+// measured on B200 (8 M particles, ms 1st/2nd half): fp64 minb 4: 7.7/6.1, 6: 5.5/5.3, 8: 4.7/4.7, 10: 5.2/6.8;
+// fp32 minb 8 unroll 4: 1.98/1.86, unroll 8: 1.90/1.78, minb 12: 2.07/1.96
+#ifndef SPHB_UNROLL_F64
+#define SPHB_UNROLL_F64 4
+#endif
+#ifndef SPHB_UNROLL_F32
+#define SPHB_UNROLL_F32 8
+#endif
+constexpr int kUnrollF64 = SPHB_UNROLL_F64, kUnrollF32 = SPHB_UNROLL_F32;
+
 namespace sphb
 {
 template <class R>
@@ -244,7 +262,7 @@ __global__ void __launch_bounds__(256)
 }
 
 template <int D, class R, bool PER>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, sizeof(R) == 8 ? SPHB_MINB_F64 : SPHB_MINB_F32)
     k_first_half(int64_t i0, int64_t n, const Rec8<R> *__restrict__ rec_a, Rec8<R> *__restrict__ rec_b, ListP<R> in,
                  ContactP<R> wall, KernelP<R> kern, KernelP<R> kern_w, PeriodicP<D, R> per, FluidP<R> fl, R dt,
                  const R *__restrict__ rho, const R *__restrict__ mass, const R *__restrict__ fprior, R *__restrict__ force,
@@ -267,7 +285,7 @@ __global__ void __launch_bounds__(128)
         {
             const u32 cnt = in.count[i];
             const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
-#pragma unroll 4
+#pragma unroll(sizeof(R) == 8 ? kUnrollF64 : kUnrollF32)
             for (u32 k = 0; k < cnt; ++k)
             {
                 u32 j = __ldg(lst + size_t(k) * 32u);
@@ -363,7 +381,7 @@ __global__ void __launch_bounds__(128)
 // Integration2ndHalf: initialization + interaction (+wall) + update in one kernel
 // ---------------------------------------------------------------------------------------------
 template <int D, class R, bool PER>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, sizeof(R) == 8 ? SPHB_MINB_F64 : SPHB_MINB_F32)
     k_second_half(int64_t i0, int64_t n, const Rec8<R> *__restrict__ rec_b, ListP<R> in, ContactP<R> wall, KernelP<R> kern,
                   KernelP<R> kern_w, PeriodicP<D, R> per, FluidP<R> fl, R dt, R *__restrict__ pos, R *__restrict__ rho,
                   R *__restrict__ drho, R *__restrict__ force)
@@ -386,7 +404,7 @@ __global__ void __launch_bounds__(128)
     {
         const u32 cnt = in.count[i];
         const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
-#pragma unroll 4
+#pragma unroll(sizeof(R) == 8 ? kUnrollF64 : kUnrollF32)
         for (u32 k = 0; k < cnt; ++k)
         {
             u32 j = __ldg(lst + size_t(k) * 32u);

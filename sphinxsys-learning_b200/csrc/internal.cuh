@@ -161,6 +161,7 @@ struct Var
     bool evolving = false;
     void *host = nullptr;
     DevBuf dev;
+    DevBuf alt; // destination of the next cell-order gather (swapped with dev; no allocation per sort)
 };
 } // namespace sphb
 
