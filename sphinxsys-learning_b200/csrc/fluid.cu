@@ -119,17 +119,16 @@ __global__ void __launch_bounds__(128)
     int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (i < i0 || i >= n)
         return;
-    const int lane = threadIdx.x & 31;
     R xi[D], Vi;
     loadXj<D, R>(xV, u32(i), xi, Vi);
     R sigma = kern.factor_W; // W0
     {
         const u32 cnt = in.count[i];
-        const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
+        const u32 *lst = listBase(in.list, in.slice_off, i);
 #pragma unroll 4
         for (u32 k = 0; k < cnt; ++k)
         {
-            u32 j = __ldg(lst + size_t(k) * 32u);
+            u32 j = listEntry(lst, k);
             R xj[D], Vj;
             loadXj<D, R>(xV, j, xj, Vj);
             periodicImage<D, R>(xi, xj, per);
@@ -151,10 +150,10 @@ __global__ void __launch_bounds__(128)
         {
             const TargetP<R> &T = ct.t[t];
             const u32 cnt = T.count[i];
-            const u32 *lst = T.list + u64(T.slice_off[i >> 5]) * 32u + lane;
+            const u32 *lst = listBase(T.list, T.slice_off, i);
             for (u32 k = 0; k < cnt; ++k)
             {
-                u32 j = __ldg(lst + size_t(k) * 32u);
+                u32 j = listEntry(lst, k);
                 R xj[D], Vj;
                 loadXj<D, R>(T.xV, j, xj, Vj);
                 R r2 = R(0);
@@ -261,6 +260,32 @@ __global__ void __launch_bounds__(256)
     stRec(rec_a, i, r8);
 }
 
+// Lane mapping of the kS-lanes-per-particle kernels: warp w of the grid owns the slice that starts at
+// particle (i0/kP)*kP + w*kP, lane l works for particle l/kS of the slice on list entries l%kS, +kS, ...
+struct GroupIdx
+{
+    int64_t i;  // particle
+    int64_t ic; // i clamped into the valid range (safe to load from)
+    int sub;    // which of the kS lanes of the particle
+    bool valid; // i is an owned particle
+};
+__device__ __forceinline__ GroupIdx groupIndex(int64_t i0, int64_t n)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5;
+    GroupIdx g;
+    g.i = (i0 / kP) * kP + warp * kP + lane / kS;
+    g.sub = lane % kS;
+    g.valid = g.i >= i0 && g.i < n;
+    g.ic = g.valid ? g.i : i0;
+    return g;
+}
+inline int groupGrid(int64_t i0, int64_t n, int block)
+{
+    int64_t slices = (n - (i0 / kP) * kP + kP - 1) / kP;
+    return int((slices * 32 + block - 1) / block);
+}
+
 template <int D, class R, bool PER>
 __global__ void __launch_bounds__(128, sizeof(R) == 8 ? SPHB_MINB_F64 : SPHB_MINB_F32)
     k_first_half(int64_t i0, int64_t n, const Rec8<R> *__restrict__ rec_a, Rec8<R> *__restrict__ rec_b, ListP<R> in,
@@ -268,92 +293,105 @@ __global__ void __launch_bounds__(128, sizeof(R) == 8 ? SPHB_MINB_F64 : SPHB_MIN
                  const R *__restrict__ rho, const R *__restrict__ mass, const R *__restrict__ fprior, R *__restrict__ force,
                  R *__restrict__ drho, R *__restrict__ vel, unsigned long long *__restrict__ max_slot)
 {
-    int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    const GroupIdx gi = groupIndex(i0, n);
     const int lane = threadIdx.x & 31;
-    R signal = R(0);
-    if (i >= i0 && i < n)
+    const int64_t i = gi.ic;
+    R ri[8], xi[D], Vi, pi, vi[D];
+    ldRec(rec_a, u32(i), ri);
+    recSplit<D, R>(ri, xi, Vi, pi, vi);
+    R f[D];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        f[a] = R(0);
+    R diss = R(0);
     {
-        R ri[8], xi[D], Vi, pi, vi[D];
-        ldRec(rec_a, u32(i), ri);
-        recSplit<D, R>(ri, xi, Vi, pi, vi);
-        const R rhoi = rho[i], mi = mass[i];
-        R f[D];
+        const u32 cnt = gi.valid ? in.count[i] : 0u;
+        const u32 *lst = in.list + u64(in.slice_off[i / kP]) * 32u + lane;
+#pragma unroll(sizeof(R) == 8 ? kUnrollF64 : kUnrollF32)
+        for (u32 e = gi.sub; e < cnt; e += kS, lst += 32)
+        {
+            u32 j = __ldg(lst);
+            R rj[8], xj[D];
+            ldRecXVp(rec_a, j, rj);
+            xj[0] = rj[0];
+            xj[1] = rj[1];
+            if (D == 3)
+                xj[D - 1] = rj[2];
+            const R Vj = rj[3], pj = rj[4];
+            if (PER)
+                periodicImage<D, R>(xi, xj, per);
+            Pair<D, R> g;
+            pairGeometry<D, R>(xi, xj, kern, g);
+            R dWV = g.dW * Vj;
+            R ps = (pi + pj) * dWV;
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+                f[a] -= ps * g.e[a];
+            diss += dissipativeUJump<R>(fl, pi - pj) * dWV;
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        f[a] = groupSum<R>(f[a]);
+    diss = groupSum<R>(diss);
+    const R rhoi = rho[i], mi = mass[i];
+    R fp[D];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        fp[a] = fprior[i * D + a];
+    R fw[D];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        fw[a] = R(0);
+    R dw = R(0);
+    if (wall.n > 0)
+    {
+        R acc_i[D];
 #pragma unroll
         for (int a = 0; a < D; ++a)
-            f[a] = R(0);
-        R diss = R(0);
+            acc_i[a] = fp[a] / mi;
+        for (int t = 0; t < wall.n; ++t)
         {
-            const u32 cnt = in.count[i];
-            const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
-#pragma unroll(sizeof(R) == 8 ? kUnrollF64 : kUnrollF32)
-            for (u32 k = 0; k < cnt; ++k)
+            const TargetP<R> &T = wall.t[t];
+            const u32 cnt = gi.valid ? T.count[i] : 0u;
+            const u32 *lst = T.list + u64(T.slice_off[i / kP]) * 32u + lane;
+            for (u32 e = gi.sub; e < cnt; e += kS, lst += 32)
             {
-                u32 j = __ldg(lst + size_t(k) * 32u);
-                R rj[8], xj[D];
-                ldRecXVp(rec_a, j, rj);
-                xj[0] = rj[0];
-                xj[1] = rj[1];
-                if (D == 3)
-                    xj[D - 1] = rj[2];
-                const R Vj = rj[3], pj = rj[4];
-                if (PER)
-                    periodicImage<D, R>(xi, xj, per);
+                u32 j = __ldg(lst);
+                R xj[D], Vj;
+                loadXj<D, R>(T.xV, j, xj, Vj);
+                R aw[D];
+                loadVec<D, R>(T.acc, j, aw);
                 Pair<D, R> g;
-                pairGeometry<D, R>(xi, xj, kern, g);
+                pairGeometry<D, R>(xi, xj, kern_w, g);
                 R dWV = g.dW * Vj;
-                R ps = (pi + pj) * dWV;
+                R face = R(0);
 #pragma unroll
                 for (int a = 0; a < D; ++a)
-                    f[a] -= ps * g.e[a];
-                diss += dissipativeUJump<R>(fl, pi - pj) * dWV;
+                    face += (acc_i[a] - aw[a]) * (-g.e[a]);
+                R p_wall = pi + rhoi * g.r * fmax(R(0), face);
+                R ps = (pi + p_wall) * dWV;
+#pragma unroll
+                for (int a = 0; a < D; ++a)
+                    fw[a] -= ps * g.e[a];
+                dw += dissipativeUJump<R>(fl, pi - p_wall) * dWV;
             }
         }
-        R fo[D], fp[D];
 #pragma unroll
         for (int a = 0; a < D; ++a)
-        {
-            fp[a] = fprior[i * D + a];
+            fw[a] = groupSum<R>(fw[a]);
+        dw = groupSum<R>(dw);
+    }
+    R signal = R(0);
+    if (gi.valid && gi.sub == 0)
+    {
+        R fo[D];
+#pragma unroll
+        for (int a = 0; a < D; ++a)
             fo[a] = force[i * D + a] + f[a] * Vi;
-        }
         R dr = diss * rhoi;
         if (wall.n > 0)
         {
-            R fw[D];
-#pragma unroll
-            for (int a = 0; a < D; ++a)
-                fw[a] = R(0);
-            R dw = R(0);
-            R acc_i[D];
-#pragma unroll
-            for (int a = 0; a < D; ++a)
-                acc_i[a] = fp[a] / mi;
-            for (int t = 0; t < wall.n; ++t)
-            {
-                const TargetP<R> &T = wall.t[t];
-                const u32 cnt = T.count[i];
-                const u32 *lst = T.list + u64(T.slice_off[i >> 5]) * 32u + lane;
-                for (u32 k = 0; k < cnt; ++k)
-                {
-                    u32 j = __ldg(lst + size_t(k) * 32u);
-                    R xj[D], Vj;
-                    loadXj<D, R>(T.xV, j, xj, Vj);
-                    R aw[D];
-                    loadVec<D, R>(T.acc, j, aw);
-                    Pair<D, R> g;
-                    pairGeometry<D, R>(xi, xj, kern_w, g);
-                    R dWV = g.dW * Vj;
-                    R face = R(0);
-#pragma unroll
-                    for (int a = 0; a < D; ++a)
-                        face += (acc_i[a] - aw[a]) * (-g.e[a]);
-                    R p_wall = pi + rhoi * g.r * fmax(R(0), face);
-                    R ps = (pi + p_wall) * dWV;
-#pragma unroll
-                    for (int a = 0; a < D; ++a)
-                        fw[a] -= ps * g.e[a];
-                    dw += dissipativeUJump<R>(fl, pi - p_wall) * dWV;
-                }
-            }
 #pragma unroll
             for (int a = 0; a < D; ++a)
                 fo[a] += fw[a] * Vi;
@@ -386,28 +424,24 @@ __global__ void __launch_bounds__(128, sizeof(R) == 8 ? SPHB_MINB_F64 : SPHB_MIN
                   KernelP<R> kern_w, PeriodicP<D, R> per, FluidP<R> fl, R dt, R *__restrict__ pos, R *__restrict__ rho,
                   R *__restrict__ drho, R *__restrict__ force)
 {
-    int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
-    if (i < i0 || i >= n)
-        return;
+    const GroupIdx gi = groupIndex(i0, n);
     const int lane = threadIdx.x & 31;
+    const int64_t i = gi.ic;
     R ri[8], xi[D], Vi, pi_unused, vi[D];
     ldRec(rec_b, u32(i), ri);
     recSplit<D, R>(ri, xi, Vi, pi_unused, vi);
-#pragma unroll
-    for (int a = 0; a < D; ++a)
-        pos[i * D + a] += vi[a] * dt * R(0.5); // fluid_integration.hpp:167-170
     R rate = R(0);
     R pd[D];
 #pragma unroll
     for (int a = 0; a < D; ++a)
         pd[a] = R(0);
     {
-        const u32 cnt = in.count[i];
-        const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
+        const u32 cnt = gi.valid ? in.count[i] : 0u;
+        const u32 *lst = in.list + u64(in.slice_off[i / kP]) * 32u + lane;
 #pragma unroll(sizeof(R) == 8 ? kUnrollF64 : kUnrollF32)
-        for (u32 k = 0; k < cnt; ++k)
+        for (u32 e = gi.sub; e < cnt; e += kS, lst += 32)
         {
-            u32 j = __ldg(lst + size_t(k) * 32u);
+            u32 j = __ldg(lst);
             R rj[8], xj[D], vj[D], Vj, pj_unused;
             ldRec(rec_b, j, rj);
             recSplit<D, R>(rj, xj, Vj, pj_unused, vj);
@@ -427,27 +461,25 @@ __global__ void __launch_bounds__(128, sizeof(R) == 8 ? SPHB_MINB_F64 : SPHB_MIN
                 pd[a] += pj * g.e[a];
         }
     }
-    const R rhoi = rho[i];
-    R dr = drho[i] + rate * rhoi;
-    R fo[D];
+    rate = groupSum<R>(rate);
 #pragma unroll
     for (int a = 0; a < D; ++a)
-        fo[a] = pd[a] * Vi;
+        pd[a] = groupSum<R>(pd[a]);
+    R rw = R(0);
+    R pw[D];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        pw[a] = R(0);
     if (wall.n > 0)
     {
-        R rw = R(0);
-        R pw[D];
-#pragma unroll
-        for (int a = 0; a < D; ++a)
-            pw[a] = R(0);
         for (int t = 0; t < wall.n; ++t)
         {
             const TargetP<R> &T = wall.t[t];
-            const u32 cnt = T.count[i];
-            const u32 *lst = T.list + u64(T.slice_off[i >> 5]) * 32u + lane;
-            for (u32 k = 0; k < cnt; ++k)
+            const u32 cnt = gi.valid ? T.count[i] : 0u;
+            const u32 *lst = T.list + u64(T.slice_off[i / kP]) * 32u + lane;
+            for (u32 e = gi.sub; e < cnt; e += kS, lst += 32)
             {
-                u32 j = __ldg(lst + size_t(k) * 32u);
+                u32 j = __ldg(lst);
                 R xj[D], Vj, vw[D], nw[D];
                 loadXj<D, R>(T.xV, j, xj, Vj);
                 loadVec<D, R>(T.vel, j, vw);
@@ -475,16 +507,35 @@ __global__ void __launch_bounds__(128, sizeof(R) == 8 ? SPHB_MINB_F64 : SPHB_MIN
                     pw[a] += pj * (sgn * nw[a]);
             }
         }
-        dr += rw * rhoi;
+        rw = groupSum<R>(rw);
 #pragma unroll
         for (int a = 0; a < D; ++a)
-            fo[a] += pw[a] * Vi;
+            pw[a] = groupSum<R>(pw[a]);
     }
-    drho[i] = dr;
+    if (gi.valid && gi.sub == 0)
+    {
 #pragma unroll
-    for (int a = 0; a < D; ++a)
-        force[i * D + a] = fo[a];
-    rho[i] = rhoi + dr * dt * R(0.5); // fluid_integration.hpp:173-176
+        for (int a = 0; a < D; ++a)
+            pos[i * D + a] += vi[a] * dt * R(0.5); // fluid_integration.hpp:167-170
+        const R rhoi = rho[i];
+        R dr = drho[i] + rate * rhoi;
+        R fo[D];
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            fo[a] = pd[a] * Vi;
+        if (wall.n > 0)
+        {
+            dr += rw * rhoi;
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+                fo[a] += pw[a] * Vi;
+        }
+        drho[i] = dr;
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            force[i * D + a] = fo[a];
+        rho[i] = rhoi + dr * dt * R(0.5); // fluid_integration.hpp:173-176
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -622,7 +673,6 @@ __global__ void __launch_bounds__(128)
     int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (i < i0 || i >= n)
         return;
-    const int lane = threadIdx.x & 31;
     R xi[D], Vi, vi[D];
     loadXj<D, R>(xV, u32(i), xi, Vi);
 #pragma unroll
@@ -634,11 +684,11 @@ __global__ void __launch_bounds__(128)
     for (int a = 0; a < D; ++a)
         f[a] = R(0);
     const u32 cnt = in.count[i];
-    const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
+    const u32 *lst = listBase(in.list, in.slice_off, i);
 #pragma unroll 2
     for (u32 k = 0; k < cnt; ++k)
     {
-        u32 j = __ldg(lst + size_t(k) * 32u);
+        u32 j = listEntry(lst, k);
         R xj[D], Vj, vj[D];
         loadXj<D, R>(xV, j, xj, Vj);
         loadVec<D, R>(vel, j, vj);
@@ -672,7 +722,6 @@ __global__ void __launch_bounds__(128)
     int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (i < i0 || i >= n)
         return;
-    const int lane = threadIdx.x & 31;
     R xi[D], Vi;
     loadXj<D, R>(xV, u32(i), xi, Vi);
     R inc[D];
@@ -680,11 +729,11 @@ __global__ void __launch_bounds__(128)
     for (int a = 0; a < D; ++a)
         inc[a] = R(0);
     const u32 cnt = in.count[i];
-    const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
+    const u32 *lst = listBase(in.list, in.slice_off, i);
 #pragma unroll 2
     for (u32 k = 0; k < cnt; ++k)
     {
-        u32 j = __ldg(lst + size_t(k) * 32u);
+        u32 j = listEntry(lst, k);
         R xj[D], Vj;
         loadXj<D, R>(xV, j, xj, Vj);
         periodicImage<D, R>(xi, xj, per);
@@ -717,7 +766,6 @@ __global__ void __launch_bounds__(128)
     int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (i < i0 || i >= n)
         return;
-    const int lane = threadIdx.x & 31;
     const R *qs[kMaxTargets] = {q0, q1, q2, q3};
     R xi[D], Vi;
     loadXj<D, R>(xV_obs, u32(i), xi, Vi);
@@ -729,10 +777,10 @@ __global__ void __launch_bounds__(128)
     {
         const TargetP<R> &T = ct.t[t];
         const u32 cnt = T.count[i];
-        const u32 *lst = T.list + u64(T.slice_off[i >> 5]) * 32u + lane;
+        const u32 *lst = listBase(T.list, T.slice_off, i);
         for (u32 k = 0; k < cnt; ++k)
         {
-            u32 j = __ldg(lst + size_t(k) * 32u);
+            u32 j = listEntry(lst, k);
             R xj[D], Vj;
             loadXj<D, R>(T.xV, j, xj, Vj);
             R r2 = R(0);
@@ -909,11 +957,11 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
     SPHB_TRY(reduceReset(ctx, 0, false));
     auto *slot = static_cast<unsigned long long *>(ctx->reduce_dev.p);
     if (P.per.mask)
-        k_first_half<D, R, true><<<gridFor(span, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_a, rec_b, listOf<R>(inner->lists[0]),
+        k_first_half<D, R, true><<<groupGrid(b->own_begin, b->own_end, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_a, rec_b, listOf<R>(inner->lists[0]),
                                                                             wp, P.kern, kern_w, P.per, fl, dt, rho, mass, fprior,
                                                                             force, drho, vel, slot);
     else
-        k_first_half<D, R, false><<<gridFor(span, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_a, rec_b, listOf<R>(inner->lists[0]),
+        k_first_half<D, R, false><<<groupGrid(b->own_begin, b->own_end, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_a, rec_b, listOf<R>(inner->lists[0]),
                                                                              wp, P.kern, kern_w, P.per, fl, dt, rho, mass, fprior,
                                                                              force, drho, vel, slot);
     SPHB_LAUNCH_CHECK(ctx);
@@ -957,12 +1005,11 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
         SPHB_LAUNCH_CHECK(ctx);
         b->rec_b_valid = (b->own_begin == 0 && b->own_end == b->n);
     }
-    const int64_t span = b->own_end - (b->own_begin & ~int64_t(31));
     if (P.per.mask)
-        k_second_half<D, R, true><<<gridFor(span, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_b, listOf<R>(inner->lists[0]), wp,
+        k_second_half<D, R, true><<<groupGrid(b->own_begin, b->own_end, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_b, listOf<R>(inner->lists[0]), wp,
                                                                              P.kern, kern_w, P.per, fl, R(dt_), pos, rho, drho, force);
     else
-        k_second_half<D, R, false><<<gridFor(span, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_b, listOf<R>(inner->lists[0]), wp,
+        k_second_half<D, R, false><<<groupGrid(b->own_begin, b->own_end, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_b, listOf<R>(inner->lists[0]), wp,
                                                                               P.kern, kern_w, P.per, fl, R(dt_), pos, rho, drho, force);
     SPHB_LAUNCH_CHECK(ctx);
     return SPHB200_OK;

@@ -112,12 +112,26 @@ struct BodyP
     PeriodicP<D, R> per;
 };
 
-// SELL-32 neighbour list of one (source, target) pair: particle i = 32*s + lane stores its k-th
-// neighbour at list[32*(slice_off[s] + k) + lane]; count[i] entries are valid.
+// Neighbour list of one (source, target) pair in a sliced-ELL layout made for kS lanes per particle:
+// a slice holds kP = 32/kS consecutive particles; entry e of particle i (slice s = i/kP) sits at
+//   list[32*(slice_off[s] + e/kS) + (i%kP)*kS + e%kS],   count[i] entries are valid.
+// A warp that gives kS lanes to each of the kP particles of a slice (lane = (i%kP)*kS + e%kS) reads 128
+// contiguous bytes per step, and the kS lanes of one particle walk ascending, mostly adjacent neighbours,
+// so the lanes of one gather instruction touch fewer distinct 128-byte lines.  Measured on B200 (8 M
+// particles, ms K2/K3): fp32 kS=1 1.86/1.76, 2 1.78/1.67, 4 2.18/2.06, 8 2.83/2.53; fp64 4.95/4.79, 4.54/4.24,
+// 4.91/4.44, 5.72/5.06 - the L1 data stage spends one wavefront per gathered 32-byte record whatever the
+// line sharing, so only kS=2 pays for its reduction shuffles.
+#ifndef SPHB_LANES
+#define SPHB_LANES 2
+#endif
+constexpr int kS = SPHB_LANES; // lanes per particle in the pair-sum kernels
+constexpr int kP = 32 / kS;    // particles per slice
+static_assert(kS == 1 || kS == 2 || kS == 4 || kS == 8, "SPHB_LANES must be 1, 2, 4 or 8");
+
 struct NeighborList
 {
     u32 *count = nullptr;     // [n_src]
-    u32 *slice_w = nullptr;   // [n_slices]  max count in the slice
+    u32 *slice_w = nullptr;   // [n_slices]  max over the slice of ceil(count/kS)
     u32 *slice_off = nullptr; // [n_slices+1] exclusive scan of slice_w (units of 32 entries)
     u32 *list = nullptr;
     size_t cap_entries = 0, cap_src = 0;
@@ -175,7 +189,7 @@ struct sphb200_ctx
     int64_t launches = 0;
     std::vector<sphb200_body *> bodies;
     std::vector<sphb200_relation *> relations;
-    sphb::DevBuf scratch_a, scratch_b, scan_tmp, reduce_dev;
+    sphb::DevBuf scratch_a, scratch_b, scan_tmp, reduce_dev, mask_buf;
     void *reduce_host = nullptr; // pinned, 64 doubles
 
     sphb200_status fail(sphb200_status s, const std::string &msg)
@@ -371,6 +385,26 @@ __device__ __forceinline__ void stRec(Rec8<double> *r, int64_t i, const double *
 {
     st256(r[i].a, v);
     st256(r[i].a + 4, v + 4);
+}
+
+// lane-per-particle view of the sliced-ELL list (kernels outside the acoustic sub-step)
+__device__ __forceinline__ const u32 *listBase(const u32 *list, const u32 *slice_off, int64_t i)
+{
+    return list + u64(__ldg(slice_off + i / kP)) * 32u + u32(i % kP) * u32(kS);
+}
+__device__ __forceinline__ u32 listEntry(const u32 *base, u32 e) { return __ldg(base + size_t(e / kS) * 32u + (e % kS)); }
+__device__ __forceinline__ u32 *listSlot(u32 *list, const u32 *slice_off, int64_t i, u32 e)
+{
+    return list + u64(slice_off[i / kP]) * 32u + u32(i % kP) * u32(kS) + size_t(e / kS) * 32u + (e % kS);
+}
+// sum / max over the kS lanes that share one particle (all 32 lanes of the warp must call)
+template <class R>
+__device__ __forceinline__ R groupSum(R v)
+{
+#pragma unroll
+    for (int o = kS / 2; o > 0; o >>= 1)
+        v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
 }
 
 template <class R>

@@ -186,9 +186,9 @@ __global__ void __launch_bounds__(128) k_search(int64_t n_src, const typename Re
         xi[1] = v.y;
         if (D == 3)
             xi[D - 1] = v.z;
-        u64 base = 0;
+        u32 *slot0 = nullptr;
         if (FILL)
-            base = u64(slice_off[i >> 5]) * 32u + u32(lane);
+            slot0 = listSlot(list, slice_off, i, 0);
         forEachCandidate<D, R>(xi, sp, cell_offset, xV_t,
                                [&](u32 j, const R *xj)
                                {
@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(128) k_search(int64_t n_src, const typename Re
                                    if (m < sp.rc2 && (!sp.inner || j != u32(i)))
                                    {
                                        if (FILL)
-                                           list[base + u64(cnt) * 32u] = j;
+                                           slot0[size_t(cnt / kS) * 32u + (cnt % kS)] = j;
                                        ++cnt;
                                    }
                                });
@@ -209,9 +209,215 @@ __global__ void __launch_bounds__(128) k_search(int64_t n_src, const typename Re
     {
         if (i < n_src)
             count[i] = cnt;
-        u32 w = __reduce_max_sync(0xffffffffu, cnt);
-        if (lane == 0 && (i >> 5) < ((n_src + 31) >> 5))
-            slice_w[i >> 5] = w;
+        u32 w = (cnt + kS - 1) / kS; // steps the kS lanes of this particle need
+#pragma unroll
+        for (int o = kP / 2; o > 0; o >>= 1)
+            w = max(w, __shfl_xor_sync(0xffffffffu, w, o));
+        if ((lane % kP) == 0 && i < n_src)
+            slice_w[i / kP] = w;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Fast path (non-periodic target, search depth 1): ONE distance pass.
+//   k_search_mask : per particle, per candidate run (the <= 3 cells along the fastest axis of each of the
+//                   3^(D-1) neighbouring cell columns are contiguous particles) a hit bit per candidate,
+//                   kRunWords 32-bit words per run; also count[i] and the slice widths.
+//   k_expand_mask : after the scan of the slice widths, turns the hit bits into the index list.
+// The second pass of the generic path (another ~474 distance tests per particle in 3-D) is replaced by
+// ~80 bit extractions.  A run longer than 32*kRunWords candidates raises the overflow flag and the host
+// falls back to the generic two-pass search.
+// ---------------------------------------------------------------------------------------------
+constexpr int kRunWords = 4;
+template <int D>
+struct MaskLayout
+{
+    static constexpr int runs = D == 3 ? 9 : 3;
+    static constexpr int words = runs * kRunWords;
+};
+
+template <int D, class R>
+__device__ __forceinline__ void runRange(const int *c, int r, const MeshP<D, R> &mesh, const u32 *__restrict__ cell_offset,
+                                         u32 &b, u32 &e)
+{
+    // run r = (dx, dy) column offset in 3-D, dx in 2-D; empty when the column is outside the mesh
+    int cc[D];
+    bool inside = true;
+    if (D == 3)
+    {
+        cc[0] = c[0] + r / 3 - 1;
+        cc[1] = c[1] + r % 3 - 1;
+        inside = cc[0] >= 0 && cc[0] < mesh.cells[0] && cc[1] >= 0 && cc[1] < mesh.cells[1];
+    }
+    else
+    {
+        cc[0] = c[0] + r - 1;
+        inside = cc[0] >= 0 && cc[0] < mesh.cells[0];
+    }
+    if (!inside)
+    {
+        b = e = 0;
+        return;
+    }
+    int lo = max(c[D - 1] - 1, 0), hi = min(c[D - 1] + 1, mesh.cells[D - 1] - 1);
+    cc[D - 1] = lo;
+    u32 first = mesh.linear(cc);
+    b = __ldg(cell_offset + first);
+    e = __ldg(cell_offset + first + u32(hi - lo) + 1);
+}
+
+template <int D, class R, bool INNER>
+__global__ void __launch_bounds__(128) k_search_mask(int64_t n_src, const typename Real4<R>::type *__restrict__ xV_s,
+                                                     const typename Real4<R>::type *__restrict__ xV_t,
+                                                     const u32 *__restrict__ cell_offset, MeshP<D, R> mesh, R rc2,
+                                                     u32 *__restrict__ count, u32 *__restrict__ slice_w,
+                                                     u32 *__restrict__ mask, int *__restrict__ overflow)
+{
+    constexpr int W = MaskLayout<D>::words;
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    u32 cnt = 0;
+    if (i < n_src)
+    {
+        typename Real4<R>::type v = ldg4(xV_s + i);
+        R xi[D];
+        xi[0] = v.x;
+        xi[1] = v.y;
+        if (D == 3)
+            xi[D - 1] = v.z;
+        int c[D];
+        mesh.cellIndex(xi, c);
+        u32 *mrow = mask + (u64(i >> 5) * W) * 32u + lane;
+        for (int r = 0; r < MaskLayout<D>::runs; ++r)
+        {
+            u32 b, e;
+            runRange<D, R>(c, r, mesh, cell_offset, b, e);
+            if (e - b > 32u * kRunWords)
+            {
+                *overflow = 1;
+                e = b + 32u * kRunWords;
+            }
+#pragma unroll
+            for (int w = 0; w < kRunWords; ++w)
+            {
+                u32 word = 0;
+                const u32 j0 = b + 32u * w;
+                if (j0 < e)
+                {
+                    const u32 m = min(e - j0, 32u);
+#pragma unroll 4
+                    for (u32 t = 0; t < m; ++t)
+                    {
+                        typename Real4<R>::type q = ldg4(xV_t + (j0 + t));
+                        R d[D];
+                        d[0] = xi[0] - q.x;
+                        d[1] = xi[1] - q.y;
+                        if (D == 3)
+                            d[D - 1] = xi[D - 1] - q.z;
+                        R mm = sqnormExact<D, R>(d);
+                        word |= (mm < rc2 ? 1u : 0u) << t;
+                    }
+                    if (INNER)
+                    { // NeighborBuilderInner: i != j (neighborhood.cpp:85-98)
+                        u32 self = u32(i) - j0;
+                        if (self < 32u)
+                            word &= ~(1u << self);
+                    }
+                }
+                mrow[u64(r * kRunWords + w) * 32u] = word;
+                cnt += __popc(word);
+            }
+        }
+        count[i] = cnt;
+    }
+    u32 w = (cnt + kS - 1) / kS;
+#pragma unroll
+    for (int o = kP / 2; o > 0; o >>= 1)
+        w = max(w, __shfl_xor_sync(0xffffffffu, w, o));
+    if ((lane % kP) == 0 && i < n_src)
+        slice_w[i / kP] = w;
+}
+
+// Rows of the sliced-ELL list are assembled in shared memory (each thread drops its particle's indices
+// into its own columns) and written out as whole 128-byte rows.  kExpandRows rows per slice are staged;
+// the rare particle with more than kExpandRows*kS neighbours writes its tail straight to global memory.
+constexpr int kExpandRows = 64;
+constexpr int kExpandBlock = 128;
+constexpr size_t kExpandSmem = size_t(kExpandBlock / 32) * kS * kExpandRows * 32 * sizeof(u32);
+
+template <int D, class R>
+__global__ void __launch_bounds__(kExpandBlock) k_expand_mask(int64_t n_src, const typename Real4<R>::type *__restrict__ xV_s,
+                                                              const u32 *__restrict__ cell_offset, MeshP<D, R> mesh,
+                                                              const u32 *__restrict__ mask, const u32 *__restrict__ slice_off,
+                                                              u32 *__restrict__ list)
+{
+    extern __shared__ u32 tile_all[];
+    constexpr int W = MaskLayout<D>::words;
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    // this warp's 32 particles = kS slices of kP particles; tile[s][row][32]
+    u32 *tile = tile_all + size_t(wid) * kS * kExpandRows * 32;
+    u32 *my = tile + size_t(lane / kP) * kExpandRows * 32 + (lane % kP) * kS;
+    if (i < n_src)
+    {
+        typename Real4<R>::type v = ldg4(xV_s + i);
+        R xi[D];
+        xi[0] = v.x;
+        xi[1] = v.y;
+        if (D == 3)
+            xi[D - 1] = v.z;
+        int c[D];
+        mesh.cellIndex(xi, c);
+        const u32 *mrow = mask + (u64(i >> 5) * W) * 32u + lane;
+        u32 *slot0 = listSlot(list, slice_off, i, 0);
+        u32 cnt = 0;
+        u32 rb[MaskLayout<D>::runs], words[W];
+#pragma unroll
+        for (int q = 0; q < W; ++q) // independent loads, all in flight at once
+            words[q] = __ldg(mrow + u64(q) * 32u);
+#pragma unroll
+        for (int r = 0; r < MaskLayout<D>::runs; ++r)
+        {
+            u32 e_unused;
+            runRange<D, R>(c, r, mesh, cell_offset, rb[r], e_unused);
+        }
+#pragma unroll
+        for (int r = 0; r < MaskLayout<D>::runs; ++r)
+        {
+#pragma unroll
+            for (int w = 0; w < kRunWords; ++w)
+            {
+                u32 word = words[r * kRunWords + w];
+                const u32 j0 = rb[r] + 32u * w;
+                while (word)
+                {
+                    u32 t = __ffs(word) - 1;
+                    word &= word - 1;
+                    const u32 row = cnt / kS, col = cnt % kS;
+                    if (row < u32(kExpandRows))
+                        my[row * 32 + col] = j0 + t;
+                    else
+                        slot0[size_t(row) * 32u + col] = j0 + t;
+                    ++cnt;
+                }
+            }
+        }
+    }
+    __syncwarp();
+    // copy out: slice s of this warp covers particles [i_warp + s*kP, +kP)
+    const int64_t i_warp = i - lane;
+#pragma unroll
+    for (int sl = 0; sl < kS; ++sl)
+    {
+        const int64_t first = i_warp + int64_t(sl) * kP;
+        if (first >= n_src)
+            break;
+        const u32 so = slice_off[first / kP];
+        const u32 rows = min(slice_off[first / kP + 1] - so, u32(kExpandRows));
+        const u32 *src = tile + size_t(sl) * kExpandRows * 32 + lane;
+        u32 *dst = list + u64(so) * 32u + lane;
+        for (u32 row = 0; row < rows; ++row)
+            dst[size_t(row) * 32u] = src[row * 32];
     }
 }
 
@@ -235,7 +441,7 @@ static sphb200_status relationUpdate(sphb200_relation *r)
     if (!src->cell_list_valid)
         return ctx->fail(SPHB200_ERR_INVALID, "relation_update: source body '" + src->name + "' has no cell list yet");
     const int64_t n = src->n;
-    const int64_t n_slices = (n + 31) / 32;
+    const int64_t n_slices = (n + kP - 1) / kP;
     BodyP<D, R> &Ps = src->P<D, R>();
     for (size_t k = 0; k < r->targets.size(); ++k)
     {
@@ -252,8 +458,8 @@ static sphb200_status relationUpdate(sphb200_relation *r)
             L.count = L.slice_w = L.slice_off = nullptr;
             size_t cap = size_t(n) + size_t(n) / 8 + 64;
             SPHB_CUDA(ctx, cudaMalloc(&L.count, cap * 4));
-            SPHB_CUDA(ctx, cudaMalloc(&L.slice_w, (cap / 32 + 2) * 4));
-            SPHB_CUDA(ctx, cudaMalloc(&L.slice_off, (cap / 32 + 3) * 4));
+            SPHB_CUDA(ctx, cudaMalloc(&L.slice_w, (cap / kP + 2) * 4));
+            SPHB_CUDA(ctx, cudaMalloc(&L.slice_off, (cap / kP + 3) * 4));
             L.cap_src = cap;
         }
         SearchP<D, R> sp;
@@ -278,20 +484,43 @@ static sphb200_status relationUpdate(sphb200_relation *r)
         auto *xs = static_cast<const typename Real4<R>::type *>(src->xV.p);
         auto *xt = static_cast<const typename Real4<R>::type *>(tgt->xV.p);
         const u32 *off = static_cast<const u32 *>(tgt->cell_offset.p);
-        k_search<D, R, false><<<gridFor(n, 128), 128, 0, st>>>(n, xs, xt, off, sp, L.count, L.slice_w, nullptr, nullptr);
-        SPHB_LAUNCH_CHECK(ctx);
-        SPHB_TRY(exclusiveScanU32(ctx, L.slice_w, L.slice_off, n_slices, true));
         unsigned long long *acc = static_cast<unsigned long long *>(ctx->reduce_dev.p) + 8;
-        SPHB_CUDA(ctx, cudaMemsetAsync(acc, 0, 8, st));
-        k_sum_u32<<<148 * 4, 256, 0, st>>>(L.count, n, acc);
-        SPHB_LAUNCH_CHECK(ctx);
-        u32 total_w = 0;
-        unsigned long long pairs = 0;
-        SPHB_CUDA(ctx, cudaMemcpyAsync(&total_w, L.slice_off + n_slices, 4, cudaMemcpyDeviceToHost, st));
-        SPHB_CUDA(ctx, cudaMemcpyAsync(&pairs, acc, 8, cudaMemcpyDeviceToHost, st));
-        SPHB_CUDA(ctx, cudaStreamSynchronize(st));
-        L.total_entries = u64(total_w) * 32u;
-        L.total_pairs = pairs;
+        int *overflow = reinterpret_cast<int *>(acc + 1);
+        bool fast = Pt.per.mask == 0 && sp.depth == 1;
+        u32 *mask = nullptr;
+        for (int attempt = 0; attempt < 2; ++attempt)
+        {
+            SPHB_CUDA(ctx, cudaMemsetAsync(acc, 0, 16, st));
+            if (fast)
+            {
+                const size_t words = size_t((n + 31) / 32) * 32u * size_t(MaskLayout<D>::words);
+                SPHB_CUDA(ctx, ctx->mask_buf.ensure(words * 4));
+                mask = static_cast<u32 *>(ctx->mask_buf.p);
+                if (r->inner)
+                    k_search_mask<D, R, true><<<gridFor(n, 128), 128, 0, st>>>(n, xs, xt, off, Pt.mesh, sp.rc2, L.count, L.slice_w, mask, overflow);
+                else
+                    k_search_mask<D, R, false><<<gridFor(n, 128), 128, 0, st>>>(n, xs, xt, off, Pt.mesh, sp.rc2, L.count, L.slice_w, mask, overflow);
+            }
+            else
+                k_search<D, R, false><<<gridFor(n, 128), 128, 0, st>>>(n, xs, xt, off, sp, L.count, L.slice_w, nullptr, nullptr);
+            SPHB_LAUNCH_CHECK(ctx);
+            SPHB_TRY(exclusiveScanU32(ctx, L.slice_w, L.slice_off, n_slices, true));
+            k_sum_u32<<<148 * 4, 256, 0, st>>>(L.count, n, acc);
+            SPHB_LAUNCH_CHECK(ctx);
+            u32 total_w = 0;
+            unsigned long long host_acc[2] = {0, 0};
+            SPHB_CUDA(ctx, cudaMemcpyAsync(&total_w, L.slice_off + n_slices, 4, cudaMemcpyDeviceToHost, st));
+            SPHB_CUDA(ctx, cudaMemcpyAsync(host_acc, acc, 16, cudaMemcpyDeviceToHost, st));
+            SPHB_CUDA(ctx, cudaStreamSynchronize(st));
+            if (fast && host_acc[1] != 0)
+            { // a candidate run did not fit the mask words: redo with the generic search
+                fast = false;
+                continue;
+            }
+            L.total_entries = u64(total_w) * 32u;
+            L.total_pairs = host_acc[0];
+            break;
+        }
         if (L.total_entries > L.cap_entries || !L.list)
         {
             cudaFree(L.list);
@@ -300,7 +529,18 @@ static sphb200_status relationUpdate(sphb200_relation *r)
             SPHB_CUDA(ctx, cudaMalloc(&L.list, cap * 4));
             L.cap_entries = cap;
         }
-        k_search<D, R, true><<<gridFor(n, 128), 128, 0, st>>>(n, xs, xt, off, sp, L.count, L.slice_w, L.slice_off, L.list);
+        if (fast)
+        {
+            static bool attr_set = false; // per (D, R) instantiation
+            if (!attr_set)
+            {
+                SPHB_CUDA(ctx, cudaFuncSetAttribute(k_expand_mask<D, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kExpandSmem)));
+                attr_set = true;
+            }
+            k_expand_mask<D, R><<<gridFor(n, kExpandBlock), kExpandBlock, kExpandSmem, st>>>(n, xs, off, Pt.mesh, mask, L.slice_off, L.list);
+        }
+        else
+            k_search<D, R, true><<<gridFor(n, 128), 128, 0, st>>>(n, xs, xt, off, sp, L.count, L.slice_w, L.slice_off, L.list);
         SPHB_LAUNCH_CHECK(ctx);
         r->target_stamp[k] = tgt->config_stamp;
     }
@@ -373,7 +613,7 @@ sphb200_status sphb200_relation_neighbors(sphb200_relation *r, int k, int32_t *c
         return SPHB200_OK;
     std::vector<u32> c, so, lst;
     c.resize(size_t(n));
-    so.resize(size_t((n + 31) / 32 + 1));
+    so.resize(size_t((n + kP - 1) / kP + 1));
     if (n > 0)
     {
         SPHB_CUDA(ctx, cudaMemcpyAsync(c.data(), L.count, size_t(n) * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -392,9 +632,9 @@ sphb200_status sphb200_relation_neighbors(sphb200_relation *r, int k, int32_t *c
             counts[i] = int32_t(c[size_t(i)]);
         if (j_out)
         {
-            u64 base = u64(so[size_t(i >> 5)]) * 32u + u64(i & 31);
+            u64 base = u64(so[size_t(i / kP)]) * 32u + u64(i % kP) * u64(kS);
             for (u32 m = 0; m < c[size_t(i)]; ++m)
-                j_out[w + m] = int64_t(lst[size_t(base + u64(m) * 32u)]);
+                j_out[w + m] = int64_t(lst[size_t(base + u64(m / kS) * 32u + (m % kS))]);
         }
         w += c[size_t(i)];
     }

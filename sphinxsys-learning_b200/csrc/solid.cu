@@ -192,15 +192,14 @@ __global__ void __launch_bounds__(128)
     int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (i < i0 || i >= n)
         return;
-    const int lane = threadIdx.x & 31;
     R xi[D], Vi;
     loadXs<D, R>(xV, u32(i), xi, Vi);
     SMat<D, R> local = SMat<D, R>::zero();
     const u32 cnt = in.count[i];
-    const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
+    const u32 *lst = listBase(in.list, in.slice_off, i);
     for (u32 k = 0; k < cnt; ++k)
     {
-        u32 j = __ldg(lst + size_t(k) * 32u);
+        u32 j = listEntry(lst, k);
         R xj[D], Vj;
         loadXs<D, R>(xV, j, xj, Vj);
         Pair<D, R> g;
@@ -286,7 +285,6 @@ __global__ void __launch_bounds__(128)
     int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (i < i0 || i >= n)
         return;
-    const int lane = threadIdx.x & 31;
     const R inv_rho0 = R(1.0) / sp.rho0, corr = R(1.07);
     R xi[D], Vi, pi[D], vi[D];
     loadXs<D, R>(xV, u32(i), xi, Vi);
@@ -305,10 +303,10 @@ __global__ void __launch_bounds__(128)
     for (int d = 0; d < D; ++d)
         f[d] = R(0);
     const u32 cnt = in.count[i];
-    const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
+    const u32 *lst = listBase(in.list, in.slice_off, i);
     for (u32 k = 0; k < cnt; ++k)
     {
-        u32 j = __ldg(lst + size_t(k) * 32u);
+        u32 j = listEntry(lst, k);
         R xj[D], Vj;
         loadXs<D, R>(xV, j, xj, Vj);
         Pair<D, R> g;
@@ -379,7 +377,6 @@ __global__ void __launch_bounds__(128)
     int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (i < i0 || i >= n)
         return;
-    const int lane = threadIdx.x & 31;
     R xi[D], Vi, vi[D];
     loadXs<D, R>(xV, u32(i), xi, Vi);
 #pragma unroll
@@ -390,10 +387,10 @@ __global__ void __launch_bounds__(128)
     }
     SMat<D, R> rate = SMat<D, R>::zero();
     const u32 cnt = in.count[i];
-    const u32 *lst = in.list + u64(in.slice_off[i >> 5]) * 32u + lane;
+    const u32 *lst = listBase(in.list, in.slice_off, i);
     for (u32 k = 0; k < cnt; ++k)
     {
-        u32 j = __ldg(lst + size_t(k) * 32u);
+        u32 j = listEntry(lst, k);
         R xj[D], Vj;
         loadXs<D, R>(xV, j, xj, Vj);
         Pair<D, R> g;
