@@ -176,6 +176,23 @@ sphb200_status sphb200_body_set_owned_pages(sphb200_body *b, int page_lo, int pa
 sphb200_status sphb200_body_owned_range(sphb200_body *b, int64_t *begin, int64_t *end);
 /* device pointers of the u32 OriginalID / SortedID arrays (valid until the next resize) */
 sphb200_status sphb200_ids_device_ptr(sphb200_body *b, void **original_id, void **sorted_id);
+/* drop every particle outside [begin, end) of the current order (the halo copies, before migration):
+ * rows [begin, end) of every variable move to the front, n becomes end-begin, ids reset to iota, the cell
+ * list is invalidated */
+sphb200_status sphb200_body_keep_range(sphb200_body *b, int64_t begin, int64_t end);
+/* index of the first particle (cell-sorted order) whose cell page along axis 0 is >= page; needs a valid
+ * cell list.  page <= 0 gives 0, page >= number of pages gives n */
+sphb200_status sphb200_body_page_begin(sphb200_body *b, int page, int64_t *out);
+/* the packed gather records of the acoustic sub-step (Rec8 = 8 Reals per particle {x,y,z,Vol|p,vx,vy,vz},
+ * which = 0: rec_a written by the 1st-half initialization, 1: rec_b written by the 1st-half update).  A
+ * slab run overwrites the records of its halo copies with the owner's between the stages. */
+sphb200_status sphb200_body_record_ptr(sphb200_body *b, int which, void **out);
+/* Dynamics1Level<Integration1stHalf...>::exec split into its two particle loops
+ * (particle_dynamics/dynamics_algorithms.h:336-352): initialization (fluid_integration.hpp:50-55), then
+ * interaction + update (:58-113), so that a slab run can refresh the halo pressures in between */
+sphb200_status sphb200_integration_1st_half_init(sphb200_relation *inner, double dt);
+sphb200_status sphb200_integration_1st_half_interact(sphb200_relation *inner, sphb200_relation *wall_or_null, int riemann, double dt);
+
 
 #ifdef __cplusplus
 }

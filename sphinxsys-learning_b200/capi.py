@@ -77,6 +77,11 @@ SIGNATURES = {
     "sphb200_body_set_owned_pages": (_i, [_vp, _i, _i]),
     "sphb200_body_owned_range": (_i, [_vp, _i64p, _i64p]),
     "sphb200_ids_device_ptr": (_i, [_vp, _vpp, _vpp]),
+    "sphb200_body_keep_range": (_i, [_vp, _i64, _i64]),
+    "sphb200_body_page_begin": (_i, [_vp, _i, _i64p]),
+    "sphb200_body_record_ptr": (_i, [_vp, _i, _vpp]),
+    "sphb200_integration_1st_half_init": (_i, [_vp, _d]),
+    "sphb200_integration_1st_half_interact": (_i, [_vp, _vp, _i, _d]),
 }
 
 

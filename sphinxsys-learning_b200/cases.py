@@ -29,8 +29,9 @@ def lattice(lo, hi, dp, dtype=np.float64):
     return np.stack([g.ravel() for g in grid], axis=1)
 
 
-def lattice_select(lo, hi, dp, dtype, keep, max_points=4_000_000):
-    """lattice(lo, hi, dp)[keep(points)] evaluated in chunks of x-planes (same order, bounded memory)"""
+def lattice_select(lo, hi, dp, dtype, keep, max_points=4_000_000, x_range=None):
+    """lattice(lo, hi, dp)[keep(points)] evaluated in chunks of x-planes (same order, bounded memory);
+    x_range = (x_lo, x_hi) keeps only the planes with x_lo <= x < x_hi (slab decomposition)"""
     lo = np.asarray(lo, dtype=dtype)
     hi = np.asarray(hi, dtype=dtype)
     dpt = dtype(dp)
@@ -39,8 +40,11 @@ def lattice_select(lo, hi, dp, dtype, keep, max_points=4_000_000):
     plane = int(np.prod(n[1:]))
     step = max(1, max_points // max(plane, 1))
     out = []
-    for x0 in range(0, int(n[0]), step):
-        grid = np.meshgrid(axes[0][x0:x0 + step], *axes[1:], indexing="ij")
+    planes = np.arange(int(n[0]))
+    if x_range is not None:
+        planes = planes[(axes[0] >= dtype(x_range[0])) & (axes[0] < dtype(x_range[1]))]
+    for k in range(0, len(planes), step):
+        grid = np.meshgrid(axes[0][planes[k:k + step]], *axes[1:], indexing="ij")
         pts = np.stack([g.ravel() for g in grid], axis=1)
         out.append(pts[keep(pts)])
     return np.concatenate(out, axis=0) if out else np.zeros((0, len(lo)), dtype)
@@ -81,7 +85,10 @@ def shell_normals(p, center, half_outer, half_inner):
 # dam break (2-D and 3-D)
 # ------------------------------------------------------------------------------------------------
 class DamBreak:
-    def __init__(self, backend, ndim=3, dp=0.05, real_bytes=8, with_observer=True, fluid_box=None, tank=None, **sys_kw):
+    def __init__(self, backend, ndim=3, dp=0.05, real_bytes=8, with_observer=True, fluid_box=None, tank=None, x_range=None,
+                 defer_configuration=False, **sys_kw):
+        """x_range: keep only the lattice planes with x in [x_lo, x_hi) (one slab of a decomposed run);
+        defer_configuration: stop before the first cell list / configuration (the slab driver finishes)"""
         dtype = np.float64 if real_bytes == 8 else np.float32
         self.ndim, self.dp = ndim, dp
         BW = dp * 4
@@ -105,9 +112,9 @@ class DamBreak:
         half_w = np.asarray(water_sz) * 0.5
         half_in = np.asarray(tank_sz) * 0.5
         half_out = half_in + BW
-        water = lattice_select(self.sys.lo, self.sys.hi, dp, dtype, lambda p: in_box(p, half_w, half_w))
+        water = lattice_select(self.sys.lo, self.sys.hi, dp, dtype, lambda p: in_box(p, half_w, half_w), x_range=x_range)
         shell = lattice_select(self.sys.lo, self.sys.hi, dp, dtype,
-                               lambda p: in_box(p, half_in, half_out) & ~in_box(p, half_in, half_in))
+                               lambda p: in_box(p, half_in, half_out) & ~in_box(p, half_in, half_in), x_range=x_range)
         vol = dtype(dp) ** ndim
         # ---- fluid body (materials/base_material.cpp:35-41: rho = rho0, m = rho0 * Vol)
         self.water = w = self.sys.add_body("WaterBody", len(water), dp)
@@ -135,6 +142,12 @@ class DamBreak:
             self.observer = o = self.sys.add_body("FluidObserver", len(probes), dp)
             o.set("Position", np.asarray(probes, dtype))
             self.obs_contact = self.sys.contact(o, [w])
+        self.time = 0.0
+        self.n_advection = 0
+        self.n_acoustic = 0
+        self.dt = 0.0
+        if defer_configuration:
+            return
         # initializeSystemCellLinkedLists / Configurations; gravity prior force (dambreak.cpp:131-136)
         w.update_cell_list()
         s.update_cell_list()

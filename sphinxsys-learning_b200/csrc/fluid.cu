@@ -914,8 +914,9 @@ static sphb200_status ensureRecBuffers(sphb200_body *b)
     return SPHB200_OK;
 }
 
+// stage bit 0: initialization (K1), bit 1: interaction + update (K2); 3 = the whole Dynamics1Level::exec
 template <int D, class R>
-static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall, int riemann, double dt_)
+static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall, int riemann, double dt_, int stage)
 {
     sphb200_ctx *ctx = inner->ctx;
     sphb200_body *b = inner->body;
@@ -927,9 +928,6 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
     BodyP<D, R> &P = b->P<D, R>();
     SPHB_TRY((ensurePacked<D, R>(b)));
     SPHB_TRY((ensureRecBuffers<D, R>(b)));
-    ContactP<R> wp;
-    KernelP<R> kern_w = P.kern;
-    SPHB_TRY((makeContactP<D, R>(wall, 4, wp, kern_w)));
     FluidP<R> fl = makeFluidP<R>(b, P.h, riemann != 0);
     R *rho, *p, *drho, *mass, *pos, *vel, *force, *fprior;
     SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
@@ -944,32 +942,44 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
     auto *xV = static_cast<const typename Real4<R>::type *>(b->xV.p);
     auto *rec_a = static_cast<Rec8<R> *>(b->rec_a.p);
     auto *rec_b = static_cast<Rec8<R> *>(b->rec_b.p);
-    const int64_t span = b->own_end - (b->own_begin & ~int64_t(31));
-    if (b->own_begin > 0 || b->own_end < b->n)
+    const bool slab = b->own_begin > 0 || b->own_end < b->n;
+    if (stage & 1)
     {
-        // slab run: the halo copies (not visited as i) still serve as neighbours j
-        k_pack_rec<D, R><<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(b->n, xV, p, vel, rec_a);
+        const int64_t span = b->own_end - (b->own_begin & ~int64_t(31));
+        if (slab && stage == 3)
+        {
+            // halo copies are not visited as i but serve as neighbours j: their records come from the
+            // named variables here; a slab driver that uses the split stages overwrites them with the
+            // owner's records between the stages instead
+            k_pack_rec<D, R><<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(b->n, xV, p, vel, rec_a);
+            SPHB_LAUNCH_CHECK(ctx);
+        }
+        k_first_half_init<D, R><<<gridFor(span, 256), 256, 0, ctx->stream>>>(b->own_begin, b->own_end, dt, fl.p0, fl.rho0, xV, rho, drho,
+                                                                           p, pos, vel, rec_a);
         SPHB_LAUNCH_CHECK(ctx);
     }
-    k_first_half_init<D, R><<<gridFor(span, 256), 256, 0, ctx->stream>>>(b->own_begin, b->own_end, dt, fl.p0, fl.rho0, xV, rho, drho, p,
-                                                                       pos, vel, rec_a);
-    SPHB_LAUNCH_CHECK(ctx);
-    SPHB_TRY(reduceReset(ctx, 0, false));
-    auto *slot = static_cast<unsigned long long *>(ctx->reduce_dev.p);
-    if (P.per.mask)
-        k_first_half<D, R, true><<<groupGrid(b->own_begin, b->own_end, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_a, rec_b, listOf<R>(inner->lists[0]),
-                                                                            wp, P.kern, kern_w, P.per, fl, dt, rho, mass, fprior,
-                                                                            force, drho, vel, slot);
-    else
-        k_first_half<D, R, false><<<groupGrid(b->own_begin, b->own_end, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_a, rec_b, listOf<R>(inner->lists[0]),
-                                                                             wp, P.kern, kern_w, P.per, fl, dt, rho, mass, fprior,
-                                                                             force, drho, vel, slot);
-    SPHB_LAUNCH_CHECK(ctx);
-    for (auto *ob : ctx->bodies)
-        ob->acoustic_max_valid = false;
-    b->acoustic_max_valid = true;
-    // rec_b now holds {x_cfg, Vol | p, v_new} of every owned particle
-    b->rec_b_valid = (b->own_begin == 0 && b->own_end == b->n);
+    if (stage & 2)
+    {
+        ContactP<R> wp;
+        KernelP<R> kern_w = P.kern;
+        SPHB_TRY((makeContactP<D, R>(wall, 4, wp, kern_w)));
+        SPHB_TRY(reduceReset(ctx, 0, false));
+        auto *slot = static_cast<unsigned long long *>(ctx->reduce_dev.p);
+        const int grid = groupGrid(b->own_begin, b->own_end, 128);
+        if (P.per.mask)
+            k_first_half<D, R, true><<<grid, 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_a, rec_b, listOf<R>(inner->lists[0]), wp,
+                                                                  P.kern, kern_w, P.per, fl, dt, rho, mass, fprior, force, drho, vel, slot);
+        else
+            k_first_half<D, R, false><<<grid, 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_a, rec_b, listOf<R>(inner->lists[0]), wp,
+                                                                   P.kern, kern_w, P.per, fl, dt, rho, mass, fprior, force, drho, vel, slot);
+        SPHB_LAUNCH_CHECK(ctx);
+        for (auto *ob : ctx->bodies)
+            ob->acoustic_max_valid = false;
+        b->acoustic_max_valid = true;
+        // rec_b now holds {x_cfg, Vol | p, v_new} of every owned particle; with the split stages the
+        // driver completes the halo records, otherwise the 2nd half re-packs them from the variables
+        b->rec_b_valid = !slab || stage != 3;
+    }
     return SPHB200_OK;
 }
 
@@ -1005,6 +1015,8 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
         SPHB_LAUNCH_CHECK(ctx);
         b->rec_b_valid = (b->own_begin == 0 && b->own_end == b->n);
     }
+    if (b->own_begin > 0 || b->own_end < b->n)
+        b->rec_b_valid = false; // one use only: the next 2nd half needs the halo records refreshed again
     if (P.per.mask)
         k_second_half<D, R, true><<<groupGrid(b->own_begin, b->own_end, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_b, listOf<R>(inner->lists[0]), wp,
                                                                              P.kern, kern_w, P.per, fl, R(dt_), pos, rho, drho, force);
@@ -1201,7 +1213,21 @@ sphb200_status sphb200_integration_1st_half(sphb200_relation *inner, sphb200_rel
     if (!inner)
         return SPHB200_ERR_INVALID;
     cudaSetDevice(inner->ctx->device);
-    return SPHB_DISPATCH(inner->ctx, firstHalf, inner, wall, riemann, dt);
+    return SPHB_DISPATCH(inner->ctx, firstHalf, inner, wall, riemann, dt, 3);
+}
+sphb200_status sphb200_integration_1st_half_init(sphb200_relation *inner, double dt)
+{
+    if (!inner)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(inner->ctx->device);
+    return SPHB_DISPATCH(inner->ctx, firstHalf, inner, nullptr, 1, dt, 1);
+}
+sphb200_status sphb200_integration_1st_half_interact(sphb200_relation *inner, sphb200_relation *wall, int riemann, double dt)
+{
+    if (!inner)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(inner->ctx->device);
+    return SPHB_DISPATCH(inner->ctx, firstHalf, inner, wall, riemann, dt, 2);
 }
 sphb200_status sphb200_integration_2nd_half(sphb200_relation *inner, sphb200_relation *wall, int riemann, double dt)
 {

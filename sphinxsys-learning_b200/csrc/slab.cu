@@ -108,6 +108,73 @@ sphb200_status sphb200_body_resize(sphb200_body *b, int64_t n_new)
     return SPHB200_OK;
 }
 
+sphb200_status sphb200_body_keep_range(sphb200_body *b, int64_t begin, int64_t end)
+{
+    if (!b || begin < 0 || end < begin || end > b->n)
+        return SPHB200_ERR_INVALID;
+    sphb200_ctx *ctx = b->ctx;
+    cudaSetDevice(ctx->device);
+    cudaStream_t st = ctx->stream;
+    const int64_t keep = end - begin;
+    if (begin > 0 && keep > 0)
+        for (auto &kv : b->vars)
+        {
+            Var &v = *kv.second;
+            size_t row = size_t(v.width) * size_t(ctx->real_bytes);
+            // through the twin buffer: source and destination ranges may overlap
+            SPHB_CUDA(ctx, v.alt.ensure(size_t(b->n) * row));
+            SPHB_CUDA(ctx, cudaMemcpyAsync(v.alt.p, static_cast<char *>(v.dev.p) + size_t(begin) * row, size_t(keep) * row,
+                                           cudaMemcpyDeviceToDevice, st));
+            std::swap(v.dev, v.alt);
+        }
+    return sphb200_body_resize(b, keep);
+}
+
+sphb200_status sphb200_body_page_begin(sphb200_body *b, int page, int64_t *out)
+{
+    if (!b || !out)
+        return SPHB200_ERR_INVALID;
+    sphb200_ctx *ctx = b->ctx;
+    if (!b->cell_list_valid)
+        return ctx->fail(SPHB200_ERR_INVALID, "body_page_begin: cell_list_update has not been called");
+    cudaSetDevice(ctx->device);
+    double info[12];
+    SPHB_TRY(sphb200_body_info(b, info));
+    int64_t per_page = 1;
+    for (int d = 1; d < ctx->ndim; ++d)
+        per_page *= int64_t(info[8 + d]);
+    const int64_t pages = int64_t(info[8]);
+    if (page <= 0 || b->n == 0)
+    {
+        *out = 0;
+        return SPHB200_OK;
+    }
+    if (page >= pages)
+    {
+        *out = b->n;
+        return SPHB200_OK;
+    }
+    u32 r = 0;
+    SPHB_CUDA(ctx, cudaMemcpyAsync(&r, static_cast<const u32 *>(b->cell_offset.p) + int64_t(page) * per_page, 4,
+                                   cudaMemcpyDeviceToHost, ctx->stream));
+    SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *out = int64_t(r);
+    return SPHB200_OK;
+}
+
+sphb200_status sphb200_body_record_ptr(sphb200_body *b, int which, void **out)
+{
+    if (!b || !out || which < 0 || which > 1)
+        return SPHB200_ERR_INVALID;
+    sphb200_ctx *ctx = b->ctx;
+    cudaSetDevice(ctx->device);
+    size_t need = size_t(b->n > 0 ? b->n : 1) * 8u * size_t(ctx->real_bytes);
+    SPHB_CUDA(ctx, b->rec_a.ensure(need));
+    SPHB_CUDA(ctx, b->rec_b.ensure(need));
+    *out = which == 0 ? b->rec_a.p : b->rec_b.p;
+    return SPHB200_OK;
+}
+
 sphb200_status sphb200_body_set_owned_pages(sphb200_body *b, int page_lo, int page_hi)
 {
     if (!b || (page_lo >= 0 && page_hi < page_lo))

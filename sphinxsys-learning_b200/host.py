@@ -104,6 +104,12 @@ class SPHSystem:
     def integration_1st_half(self, inner, wall=None, riemann=True, dt=0.0):
         self.check(self.lib.sphb200_integration_1st_half(inner.h, wall.h if wall else None, int(riemann), dt))
 
+    def integration_1st_half_init(self, inner, dt=0.0):
+        self.check(self.lib.sphb200_integration_1st_half_init(inner.h, dt))
+
+    def integration_1st_half_interact(self, inner, wall=None, riemann=True, dt=0.0):
+        self.check(self.lib.sphb200_integration_1st_half_interact(inner.h, wall.h if wall else None, int(riemann), dt))
+
     def integration_2nd_half(self, inner, wall=None, riemann=True, dt=0.0):
         self.check(self.lib.sphb200_integration_2nd_half(inner.h, wall.h if wall else None, int(riemann), dt))
 
@@ -269,6 +275,20 @@ class Body:
         b, e = C.c_int64(), C.c_int64()
         self.sys.check(self.lib.sphb200_body_owned_range(self.h, C.byref(b), C.byref(e)))
         return b.value, e.value
+
+    def keep_range(self, begin, end):
+        self.sys.check(self.lib.sphb200_body_keep_range(self.h, int(begin), int(end)))
+        self.n = int(end) - int(begin)
+
+    def page_begin(self, page):
+        out = C.c_int64()
+        self.sys.check(self.lib.sphb200_body_page_begin(self.h, int(page), C.byref(out)))
+        return out.value
+
+    def record_ptr(self, which):
+        p = C.c_void_p()
+        self.sys.check(self.lib.sphb200_body_record_ptr(self.h, int(which), C.byref(p)))
+        return p.value
 
     def ids_device_ptr(self):
         a, b = C.c_void_p(), C.c_void_p()

@@ -1,0 +1,365 @@
+"""Slab decomposition of the dam-break path over several GPUs (the reference is single-address-space).
+
+1-D slabs along x.  x is the slowest index of the linear cell index (meshes/base_mesh.hxx:68-78), so the
+cell pages [page_lo, page_hi) a rank owns are one contiguous run of its cell-sorted particles, and the
+two pages next to it (one cut-off radius each) are its halo.  Every rank uses the GLOBAL mesh, so cell
+indices, neighbour sets and sums are those of the single-GPU run.
+
+Per acoustic sub-step:  1st-half initialization -> halo records rec_a (new p) from the owners -> 1st-half
+interaction+update -> halo records rec_b (new v) -> 2nd half -> min all-reduce of dt.
+Per advection step:     one exchange that carries migrating particles AND the fresh halo (each rank
+sends its particles lying in the two pages either side of a cut), then sort + relations + halo index maps.
+
+The ranks' kernels are libsphb200's (host.py); torch is the plumbing only: views of device memory,
+index_select/index_copy_ for the halo pack/unpack, torch.distributed (NCCL) send/recv and all-reduce.
+`LocalComm` runs all slabs inside one process on one GPU (tests, single-GPU boxes); `DistComm` is one
+slab per process.
+"""
+import math
+
+import numpy as np
+
+from . import cases
+
+try:
+    import torch
+    import torch.distributed as dist
+except Exception:  # pragma: no cover - torch is part of the image
+    torch = None
+    dist = None
+
+
+class _Raw:
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"data": (int(ptr), False), "shape": tuple(shape), "typestr": typestr, "version": 2}
+
+
+def dev_tensor(ptr, shape, np_dtype, device):
+    """torch view of raw device memory owned by libsphb200"""
+    if int(np.prod(shape)) == 0:
+        return torch.empty(tuple(shape), dtype=torch.from_numpy(np.zeros(0, np_dtype)).dtype, device=device)
+    return torch.as_tensor(_Raw(ptr, shape, np.dtype(np_dtype).str), device=device)
+
+
+# ------------------------------------------------------------------------------------------------
+# page cuts (pure host logic, tested on CPU)
+# ------------------------------------------------------------------------------------------------
+def page_cuts(fluid_per_page, n_slabs):
+    """cut pages so every slab owns ~the same number of fluid particles.
+    returns n_slabs+1 page indices, first 0, last len(fluid_per_page)"""
+    c = np.concatenate([[0], np.cumsum(np.asarray(fluid_per_page, dtype=np.int64))])
+    total = int(c[-1])
+    cuts = [0]
+    for r in range(1, n_slabs):
+        target = total * r / n_slabs
+        p = int(np.searchsorted(c, target, side="left"))
+        # pick the nearer page boundary, keep cuts strictly increasing
+        if p > 0 and abs(c[p - 1] - target) <= abs(c[min(p, len(c) - 1)] - target):
+            p -= 1
+        cuts.append(max(p, cuts[-1] + 1))
+    cuts.append(len(fluid_per_page))
+    return cuts
+
+
+def match_by_gid(send_gid, recv_gid):
+    """orders that make sender rows and receiver slots line up: both sides sort by global id"""
+    return np.argsort(send_gid, kind="stable"), np.argsort(recv_gid, kind="stable")
+
+
+# ------------------------------------------------------------------------------------------------
+# communicators: exchange(list over local parts of (to_left, to_right)) -> list of (from_left, from_right)
+# ------------------------------------------------------------------------------------------------
+class LocalComm:
+    """all slabs in this process (one GPU): neighbours are list neighbours, the 'transfer' is a clone"""
+
+    def __init__(self, n_slabs):
+        self.n_slabs, self.rank0, self.world = n_slabs, 0, 1
+
+    def local_slabs(self):
+        return list(range(self.n_slabs))
+
+    def exchange(self, sends):
+        out = []
+        for k in range(self.n_slabs):
+            from_left = sends[k - 1][1].clone() if k > 0 else None
+            from_right = sends[k + 1][0].clone() if k + 1 < self.n_slabs else None
+            out.append((from_left, from_right))
+        return out
+
+    exchange_fixed = None  # same as exchange (sizes are implicit in-process)
+
+    def allreduce(self, values, op):
+        v = min(values) if op == "min" else (max(values) if op == "max" else sum(values))
+        return v
+
+    def barrier(self):
+        pass
+
+
+class DistComm:
+    """one slab per process over torch.distributed (NCCL): rank r owns slab r"""
+
+    def __init__(self, device):
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.n_slabs, self.device = self.world, device
+
+    def local_slabs(self):
+        return [self.rank]
+
+    def exchange(self, sends):
+        to_left, to_right = sends[0]
+        left = self.rank - 1 if self.rank > 0 else None
+        right = self.rank + 1 if self.rank + 1 < self.world else None
+        # row counts first (the payload shapes differ every advection step)
+        cnt_out = torch.tensor([to_left.shape[0] if left is not None else 0, to_right.shape[0] if right is not None else 0],
+                               dtype=torch.int64, device=self.device)
+        cnt_in = torch.zeros(2, dtype=torch.int64, device=self.device)
+        ops = []
+        if left is not None:
+            ops += [dist.P2POp(dist.isend, cnt_out[0:1], left), dist.P2POp(dist.irecv, cnt_in[0:1], left)]
+        if right is not None:
+            ops += [dist.P2POp(dist.isend, cnt_out[1:2], right), dist.P2POp(dist.irecv, cnt_in[1:2], right)]
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        n_left, n_right = (int(x) for x in cnt_in.tolist())
+        from_left = from_right = None
+        ops = []
+        if left is not None:
+            from_left = torch.empty((n_left,) + tuple(to_left.shape[1:]), dtype=to_left.dtype, device=self.device)
+            ops += [dist.P2POp(dist.isend, to_left.contiguous(), left), dist.P2POp(dist.irecv, from_left, left)]
+        if right is not None:
+            from_right = torch.empty((n_right,) + tuple(to_right.shape[1:]), dtype=to_right.dtype, device=self.device)
+            ops += [dist.P2POp(dist.isend, to_right.contiguous(), right), dist.P2POp(dist.irecv, from_right, right)]
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        return [(from_left, from_right)]
+
+    def exchange_fixed(self, sends, recv_rows):
+        """payload whose row counts both sides already know (the per-sub-step halo records)"""
+        to_left, to_right = sends[0]
+        n_left, n_right = recv_rows[0]
+        left = self.rank - 1 if self.rank > 0 else None
+        right = self.rank + 1 if self.rank + 1 < self.world else None
+        from_left = from_right = None
+        ops = []
+        if left is not None:
+            from_left = torch.empty((n_left,) + tuple(to_left.shape[1:]), dtype=to_left.dtype, device=self.device)
+            ops += [dist.P2POp(dist.isend, to_left, left), dist.P2POp(dist.irecv, from_left, left)]
+        if right is not None:
+            from_right = torch.empty((n_right,) + tuple(to_right.shape[1:]), dtype=to_right.dtype, device=self.device)
+            ops += [dist.P2POp(dist.isend, to_right, right), dist.P2POp(dist.irecv, from_right, right)]
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        return [(from_left, from_right)]
+
+    def allreduce(self, values, op):
+        t = torch.tensor([values[0]], dtype=torch.float64, device=self.device)
+        dist.all_reduce(t, op={"min": dist.ReduceOp.MIN, "max": dist.ReduceOp.MAX, "sum": dist.ReduceOp.SUM}[op])
+        return float(t.item())
+
+    def barrier(self):
+        dist.barrier()
+
+
+def _exchange_fixed(comm, sends, recv_rows):
+    if getattr(comm, "exchange_fixed", None):
+        return comm.exchange_fixed(sends, recv_rows)
+    return comm.exchange(sends)
+
+
+# ------------------------------------------------------------------------------------------------
+# the decomposed 3-D dam break
+# ------------------------------------------------------------------------------------------------
+MIGRATE_VARS = ["Position", "VolumetricMeasure", "Mass", "Density", "Pressure", "DensityChangeRate", "Velocity", "Force",
+                "ForcePrior", "PreviousGravityForce", "GlobalID"]
+
+
+class _Part:
+    """one slab: a DamBreak restricted to its pages +- one halo page, on its own context"""
+    pass
+
+
+class SlabDamBreak:
+    """tests/3d_examples/test_3d_dambreak/dambreak.cpp:159-195 over n_slabs slabs; same loop as cases.DamBreak"""
+
+    def __init__(self, backend, comm, dp=0.05, real_bytes=8, device=0, stream=None, ndim=3):
+        assert torch is not None
+        self.comm, self.dp, self.ndim, self.real_bytes = comm, dp, ndim, real_bytes
+        self.device = torch.device("cuda", device)
+        self.np_real = np.float64 if real_bytes == 8 else np.float32
+        self.np_int = np.int64 if real_bytes == 8 else np.int32
+        self.t_int = torch.int64 if real_bytes == 8 else torch.int32
+        if stream is None:
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        # ---- global mesh (query the library with an empty probe case) and the page cuts
+        probe = cases.DamBreak(backend, ndim=ndim, dp=dp, real_bytes=real_bytes, with_observer=False, x_range=(1e30, 2e30),
+                               defer_configuration=True, device=device, stream=stream)
+        info = probe.water.info()
+        self.mesh_lo, self.spacing, self.cells = info["mesh_lo"], info["spacing"], info["cells"]
+        self.sys_lo = probe.sys.lo.copy()
+        self.U_ref, self.gravity = probe.U_ref, probe.gravity
+        n_lat = np.ceil((probe.sys.hi - probe.sys.lo) / dp).astype(np.int64)
+        self.n_lat = n_lat
+        xs = probe.sys.lo[0] + (np.arange(n_lat[0]) + 0.5) * dp
+        in_fluid = (xs >= 0.0) & (xs <= 2.0)
+        page_of = np.clip(np.floor((xs - self.mesh_lo[0]) / self.spacing).astype(np.int64), 0, self.cells[0] - 1)
+        fluid_per_page = np.bincount(page_of[in_fluid], minlength=self.cells[0])
+        probe.sys.close()
+        self.cuts = page_cuts(fluid_per_page, comm.n_slabs)
+        # ---- the local slabs
+        self.parts = []
+        for r in comm.local_slabs():
+            P = _Part()
+            P.rank, P.p_lo, P.p_hi = r, self.cuts[r], self.cuts[r + 1]
+            P.has_left, P.has_right = r > 0, r + 1 < comm.n_slabs
+            x_lo = self.mesh_lo[0] + (P.p_lo - 1) * self.spacing - dp
+            x_hi = self.mesh_lo[0] + (P.p_hi + 1) * self.spacing + dp
+            P.case = c = cases.DamBreak(backend, ndim=ndim, dp=dp, real_bytes=real_bytes, with_observer=False,
+                                        x_range=(x_lo, x_hi), defer_configuration=True, device=device, stream=stream)
+            w, s = c.water, c.wall
+            pos = w.get("Position").astype(np.float64) if w.n else np.zeros((0, ndim))
+            idx = np.rint((pos - self.sys_lo) / dp - 0.5).astype(np.int64)
+            gid = idx[:, 0]
+            for d in range(1, ndim):
+                gid = gid * int(n_lat[d]) + idx[:, d]
+            w.set("GlobalID", gid.astype(self.np_int).view(self.np_real))  # bit pattern, moved verbatim by the sort
+            for nm, wd in (("DensitySummation", 1), ("GravityForce", ndim)):
+                w.register(nm, wd, False)
+            # trim both bodies to pages [p_lo-1, p_hi+1) exactly, then own [p_lo, p_hi)
+            for body in (w, s):
+                body.update_cell_list()
+                a, b = body.page_begin(P.p_lo - 1), body.page_begin(P.p_hi + 1)
+                body.keep_range(a, b)
+            w.set_owned_pages(P.p_lo, P.p_hi)
+            w.update_cell_list()
+            s.update_cell_list()
+            c.update_configuration(observer=False)
+            c.sys.gravity_force(w, c.gravity)
+            self.parts.append(P)
+        self._halo_maps()
+        self.time, self.dt, self.n_advection, self.n_acoustic = 0.0, 0.0, 0, 0
+
+    # ---- views ----------------------------------------------------------------------------------
+    def _var(self, P, name):
+        w = P.case.water
+        width = w.width(name)
+        return dev_tensor(w.device_ptr(name), (w.n, width), self.np_real, self.device)
+
+    def _gid(self, P):
+        return self._var(P, "GlobalID").view(self.t_int).reshape(-1)
+
+    def _halo_maps(self):
+        """index lists (sorted by global id on both sides) for the per-sub-step halo record exchange"""
+        for P in self.parts:
+            w = P.case.water
+            ob, oe = w.owned_range()
+            P.ob, P.oe = ob, oe
+            gid = self._gid(P)
+            e1 = w.page_begin(P.p_lo + 1) if P.has_left else ob       # owned particles of my first page
+            b1 = w.page_begin(P.p_hi - 1) if P.has_right else oe      # owned particles of my last page
+            e1, b1 = min(max(e1, ob), oe), min(max(b1, ob), oe)
+            P.send_left = (ob + torch.argsort(gid[ob:e1], stable=True)) if P.has_left else None
+            P.send_right = (b1 + torch.argsort(gid[b1:oe], stable=True)) if P.has_right else None
+            P.recv_left = torch.argsort(gid[0:ob], stable=True) if P.has_left else None
+            P.recv_right = (oe + torch.argsort(gid[oe:w.n], stable=True)) if P.has_right else None
+            P.rec = [dev_tensor(w.record_ptr(k), (w.n, 8), self.np_real, self.device) for k in (0, 1)]
+
+    def _halo_records(self, which):
+        sends, rows = [], []
+        for P in self.parts:
+            rec = P.rec[which]
+            sends.append((rec.index_select(0, P.send_left) if P.has_left else None,
+                          rec.index_select(0, P.send_right) if P.has_right else None))
+            rows.append((P.recv_left.numel() if P.has_left else 0, P.recv_right.numel() if P.has_right else 0))
+        recvs = _exchange_fixed(self.comm, sends, rows)
+        for P, (fl, fr) in zip(self.parts, recvs):
+            if P.has_left:
+                P.rec[which].index_copy_(0, P.recv_left, fl)
+            if P.has_right:
+                P.rec[which].index_copy_(0, P.recv_right, fr)
+
+    # ---- the loop ---------------------------------------------------------------------------------
+    def _min_over_slabs(self, fn):
+        vals = []
+        for P in self.parts:
+            vals.append(fn(P) if P.oe > P.ob else math.inf)
+        return self.comm.allreduce(vals, "min")
+
+    def acoustic_substep(self, dt):
+        for P in self.parts:
+            P.case.sys.integration_1st_half_init(P.case.inner, dt)
+        self._halo_records(0)
+        for P in self.parts:
+            P.case.sys.integration_1st_half_interact(P.case.inner, P.case.wall_contact, True, dt)
+        self._halo_records(1)
+        for P in self.parts:
+            P.case.sys.integration_2nd_half(P.case.inner, P.case.wall_contact, True, dt)
+        self.n_acoustic += 1
+
+    def advection_step(self):
+        Dt = self._min_over_slabs(lambda P: P.case.sys.advection_dt(P.case.water, self.U_ref))
+        for P in self.parts:
+            P.case.sys.density_summation(P.case.inner, P.case.wall_contact, free_surface=True)
+        relaxation, k = 0.0, 0
+        while relaxation < Dt:  # dambreak.cpp:168-177: step with the previous dt, then reduce
+            self.acoustic_substep(self.dt)
+            self.dt = self._min_over_slabs(lambda P: P.case.sys.acoustic_dt(P.case.water))
+            relaxation += self.dt
+            self.time += self.dt
+            k += 1
+        self.n_advection += 1
+        self.reconfigure()
+        return Dt, k
+
+    def reconfigure(self):
+        """migration + fresh halo in one exchange, then sort, relations and halo maps"""
+        sends = []
+        for P in self.parts:
+            w = P.case.water
+            w.keep_range(P.ob, P.oe)          # drop the old halo copies
+            w.update_cell_list()              # owned particles by their new cells
+            a = w.page_begin(P.p_lo + 1) if P.has_left else 0      # pages <= p_lo: migrants to / halo of the left slab
+            b = w.page_begin(P.p_hi - 1) if P.has_right else w.n   # pages >= p_hi-1: same for the right slab
+            cols = [self._var(P, nm) for nm in MIGRATE_VARS]
+            sends.append((torch.cat([c[0:a] for c in cols], dim=1) if P.has_left else None,
+                          torch.cat([c[b:w.n] for c in cols], dim=1) if P.has_right else None))
+        recvs = self.comm.exchange(sends)
+        for P, (fl, fr) in zip(self.parts, recvs):
+            w = P.case.water
+            n_old = w.n
+            extra = [t for t in (fl, fr) if t is not None and t.shape[0] > 0]
+            n_new = n_old + sum(t.shape[0] for t in extra)
+            w.resize(n_new)
+            if extra:
+                block = torch.cat(extra, dim=0)
+                col = 0
+                for nm in MIGRATE_VARS:
+                    v = self._var(P, nm)
+                    v[n_old:n_new] = block[:, col:col + v.shape[1]]
+                    col += v.shape[1]
+            w.update_cell_list()
+            P.case.update_configuration(observer=False)
+        self._halo_maps()
+
+    # ---- observables / inspection -------------------------------------------------------------------
+    def n_fluid(self):
+        return int(self.comm.allreduce([float(sum(P.oe - P.ob for P in self.parts))], "sum"))
+
+    def mechanical_energy(self):
+        vals = [P.case.sys.total_mechanical_energy(P.case.water, self.gravity) if P.oe > P.ob else 0.0 for P in self.parts]
+        return self.comm.allreduce([sum(vals)], "sum")
+
+    def owned(self, name):
+        """(global ids, values) of the locally owned particles, on the host"""
+        ids, vals = [], []
+        for P in self.parts:
+            torch.cuda.synchronize()
+            ids.append(self._gid(P)[P.ob:P.oe].cpu().numpy().astype(np.int64))
+            vals.append(self._var(P, name)[P.ob:P.oe].cpu().numpy())
+        return np.concatenate(ids), np.concatenate(vals, axis=0)
+
+    def launches(self):
+        return sum(P.case.sys.launches for P in self.parts)

@@ -1,0 +1,119 @@
+"""Slab decomposition.  The reference has no multi-device semantics to match, so the
+parity statement is: an N-slab run equals the single-GPU run on identical inputs (per-particle fields
+keyed by the global lattice id, counts, dt sequence), and the single-GPU run is pinned to the oracle by
+test_gpu_parity.py.  Host logic (page cuts, id matching, the send/recv protocol over gloo with
+world_size 2) runs without a GPU."""
+import importlib
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def slab():
+    importlib.import_module("sphinxsys-learning_b200")
+    return importlib.import_module("sphinxsys-learning_b200.slab")
+
+
+def test_page_cuts_balance_and_cover(slab):
+    per_page = [0, 0, 7, 7, 7, 7, 7, 7, 7, 7, 0, 0, 0]
+    for n in (1, 2, 4, 8):
+        cuts = slab.page_cuts(per_page, n)
+        assert cuts[0] == 0 and cuts[-1] == len(per_page) and len(cuts) == n + 1
+        assert all(b > a for a, b in zip(cuts, cuts[1:]))
+        owned = [sum(per_page[a:b]) for a, b in zip(cuts, cuts[1:])]
+        assert sum(owned) == sum(per_page)
+        assert max(owned) - min(owned) <= 7
+    # more slabs than fluid pages still gives a valid (if unbalanced) cover
+    cuts = slab.page_cuts([0, 5, 5, 0], 4)
+    assert cuts == sorted(cuts) and len(set(cuts)) == 5
+
+
+def test_match_by_gid(slab):
+    rng = np.random.default_rng(3)
+    gid = rng.permutation(1000)[:200]
+    send = rng.permutation(gid)
+    recv = rng.permutation(gid)
+    si, ri = slab.match_by_gid(send, recv)
+    assert np.array_equal(send[si], recv[ri])
+
+
+WORKER = r'''
+import importlib, os, sys
+sys.path.insert(0, sys.argv[1])
+import torch, torch.distributed as dist
+importlib.import_module("sphinxsys-learning_b200")
+slab = importlib.import_module("sphinxsys-learning_b200.slab")
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:" + sys.argv[2], rank=int(sys.argv[3]), world_size=2)
+comm = slab.DistComm(torch.device("cpu"))
+r = comm.rank
+assert comm.local_slabs() == [r]
+# variable-size exchange (migration + halo): rank 0 sends 3 rows right, rank 1 sends 5 rows left
+to_left = torch.full((5 if r == 1 else 0, 4), float(10 + r))
+to_right = torch.full((3 if r == 0 else 0, 4), float(20 + r))
+(fl, fr), = comm.exchange([(to_left, to_right)])
+if r == 0:
+    assert fl is None and fr.shape == (5, 4) and float(fr[0, 0]) == 11.0
+else:
+    assert fr is None and fl.shape == (3, 4) and float(fl[0, 0]) == 20.0
+# fixed-size exchange (halo records)
+(fl, fr), = comm.exchange_fixed([(torch.full((2, 8), float(r)), torch.full((2, 8), float(r)))], [(2, 2)])
+other = fr if r == 0 else fl
+assert other.shape == (2, 8) and float(other[0, 0]) == float(1 - r)
+assert comm.allreduce([float(r + 1)], "min") == 1.0 and comm.allreduce([float(r + 1)], "sum") == 3.0
+dist.destroy_process_group()
+print("ok", r)
+'''
+
+
+def test_dist_comm_protocol_over_gloo(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER)
+    port = str(29500 + os.getpid() % 2000)
+    procs = [subprocess.Popen([sys.executable, str(script), ROOT, port, str(r)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+             for r in range(2)]
+    outs = [p.communicate(timeout=300)[0].decode() for p in procs]
+    for r, (p, o) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0 and f"ok {r}" in o, o
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_slabs,real_bytes", [(2, 8), (3, 8), (2, 4)])
+def test_slabs_equal_single_gpu(pk, gpu, slab, n_slabs, real_bytes):
+    """N slabs emulated in one process (LocalComm) against the undecomposed run"""
+    dp, steps = 0.05, 6
+    one = pk.cases.DamBreak(gpu, ndim=3, dp=dp, real_bytes=real_bytes, with_observer=False)
+    many = slab.SlabDamBreak(gpu, slab.LocalComm(n_slabs), dp=dp, real_bytes=real_bytes)
+    assert many.n_fluid() == one.water.n
+    assert sum(1 for P in many.parts if P.oe > P.ob) == n_slabs  # every slab owns fluid
+    # global ids of the single run, from its initial lattice
+    pos0 = one.water.get("Position").astype(np.float64)
+    oid0, _ = one.water.ids()
+    idx = np.rint((pos0 - many.sys_lo) / dp - 0.5).astype(np.int64)
+    gid_sorted = (idx[:, 0] * int(many.n_lat[1]) + idx[:, 1]) * int(many.n_lat[2]) + idx[:, 2]
+    gid_by_oid = np.empty_like(gid_sorted)
+    gid_by_oid[oid0] = gid_sorted
+    for s in range(steps):
+        r1, rn = one.advection_step(), many.advection_step()
+        assert r1[1] == rn[1]
+        assert r1[0] == rn[0]  # max-type reductions are order independent: bit-exact dt
+    assert many.n_fluid() == one.water.n
+    tol = 1e-9 if real_bytes == 8 else 1e-4
+    oid, _ = one.water.ids()
+    for name in ("Position", "Velocity", "Density", "Pressure", "DensityChangeRate", "Force"):
+        ref = one.water.get(name)
+        ref_by_gid = dict()
+        order = np.argsort(gid_by_oid[oid])
+        g, v = many.owned(name)
+        o2 = np.argsort(g)
+        assert np.array_equal(gid_by_oid[oid][order], g[o2])
+        a, b = v[o2].astype(np.float64).reshape(len(g), -1), ref[order].astype(np.float64).reshape(len(g), -1)
+        err = np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
+        assert err < tol, (name, err)
+    e1, en = one.mechanical_energy(), many.mechanical_energy()
+    assert abs(e1 - en) <= 1e-9 * abs(e1) if real_bytes == 8 else abs(e1 - en) <= 1e-4 * abs(e1)
