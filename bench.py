@@ -93,6 +93,132 @@ def cpu_reference_run(dp, steps, warmup):
                       f"({sub} acoustic sub-steps) in {dt:.1f} s, OpenMP CPU restatement of the classic stored-neighbourhood algorithm"}, dt / max(steps, 1)
 
 
+def slab_dp(dp1, world):
+    """weak scaling: the same tank at a finer spacing, so every GPU keeps ~the single-GPU particle count
+    (dp = 1/272 -> 20.1 M fluid particles on 1 GPU, 1/544 -> 161 M on 8; BASELINE.json configs[3])"""
+    return 1.0 / round((1.0 / dp1) * world ** (1.0 / 3.0))
+
+
+def slab_main(a, pk, stream, rank, world, local_rank, warmup):
+    """N > 1: one x-slab per GPU with halo exchange + migration over NCCL; no replicas."""
+    import torch
+    import torch.distributed as dist
+    from importlib import import_module
+    slab = import_module("sphinxsys-learning_b200.slab")
+    dp = slab_dp(a.dp, world)
+    t_build = time.perf_counter()
+    comm = slab.DistComm(torch.device("cuda", local_rank))
+    case = slab.SlabDamBreak(pk.host, comm, dp=dp, real_bytes=a.real, device=local_rank, stream=stream.cuda_stream)
+    t_build = time.perf_counter() - t_build
+    P = case.parts[0]
+    n_f = case.n_fluid()
+    R = a.real
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sub0, l0 = case.n_acoustic, case.launches()
+        t0 = time.perf_counter()
+        ev0.record(stream)
+        for _ in range(steps):
+            fn()
+        ev1.record(stream)
+        barrier()
+        ms = max(ev0.elapsed_time(ev1), 0.0)
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        t = torch.tensor([ms, wall_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0].item()), float(t[1].item()), case.n_acoustic - sub0, case.launches() - l0
+
+    for _ in range(warmup):
+        case.advection_step()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ms_max, _, sub, launches = timed(case.advection_step, a.steps)
+    clocks = sampler.stop() if sampler else None
+    value = n_f * sub / (ms_max * 1e-3)
+
+    # ---- roofline of the dominant kernel on this rank's slab (owned particles as i) ----
+    w = P.case.water
+    owned = P.oe - P.ob
+    pairs = int(P.case.inner.neighbors()[0][P.ob:P.oe].sum()) + int(P.case.wall_contact.neighbors()[0][P.ob:P.oe].sum())
+    alg_bytes = owned * 20 * R + 4 * pairs
+    reps = 5
+    S = P.case.sys
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    S.integration_2nd_half(P.case.inner, P.case.wall_contact, True, 0.0)
+    torch.cuda.synchronize()
+    k0.record(stream)
+    for _ in range(reps):
+        S.integration_2nd_half(P.case.inner, P.case.wall_contact, True, 0.0)
+    k1.record(stream)
+    torch.cuda.synchronize()
+    k_ms = k0.elapsed_time(k1) / reps
+    peak, peak_src = peaks()
+    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_second_half (Integration2ndHalf inner+wall) on rank 0's slab",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg_bytes,
+                "pairs_per_particle": pairs / max(owned, 1)}
+    a_step = 56 * R + 2 * 4 * pairs / max(owned, 1)
+    step_frac = a_step * value / world / 1e9 / peak
+
+    # ---- e2e: every step the slab's evolving state comes from pinned host arrays and goes back ----
+    e2e = None
+    if not a.no_e2e:
+        import ctypes as C
+        names = [nm for nm in slab.MIGRATE_VARS]
+        cap = int(w.n * 1.3) + 1024
+        host = {nm: torch.empty((cap, w.width(nm)), dtype=torch.float64 if R == 8 else torch.float32).pin_memory()
+                for nm in names}
+        lib = S.lib
+
+        def download():
+            for nm, ten in host.items():
+                S.check(lib.sphb200_var_download(w.h, nm.encode(), C.c_void_p(ten.data_ptr())))
+
+        def upload():
+            for nm, ten in host.items():
+                S.check(lib.sphb200_var_upload(w.h, nm.encode(), C.c_void_p(ten.data_ptr())))
+
+        moved = [0, 0]
+
+        def e2e_step():
+            assert w.n <= cap
+            moved[0] += sum(w.n * t.shape[1] * t.element_size() for t in host.values())
+            upload()
+            case.advection_step()  # ends with migration + halo + sort + relations (reconfigure)
+            case.mechanical_energy()
+            moved[1] += sum(w.n * t.shape[1] * t.element_size() for t in host.values()) + 8
+            download()
+
+        download()
+        e2e_step()
+        moved[:] = [0, 0]
+        ms_e, wall_e, sub_e, _ = timed(e2e_step, a.steps)
+        e2e = {"value": n_f * sub_e / (max(ms_e, wall_e) * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": int(moved[0] // a.steps) * world, "d2h_bytes_per_step": int(moved[1] // a.steps) * world,
+               "note": "per rank: the slab's evolving fluid state (owned + halo rows) is uploaded from pinned host arrays before the "
+                       "advection step and downloaded after it, plus the all-reduced mechanical energy; bytes are rank 0's x N"}
+
+    if rank == 0:
+        out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": warmup,
+               "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+               "dtype": "f64" if R == 8 else "f32", "data": "synthetic",
+               "config": {"workload": f"test_3d_dambreak lattice dp=1/{round(1 / dp)}: {n_f} fluid particles over {world} x-slabs "
+                                      f"(rank 0: {owned} owned + {w.n - owned} halo fluid, {P.case.wall.n} wall)",
+                          "acoustic_substeps": sub, "advection_steps": a.steps, "l2": "inputs larger than L2",
+                          "parallelism": f"{world} slabs along x, NCCL halo records per sub-step + migration per advection step",
+                          "page_cuts": [int(c) for c in case.cuts], "build_seconds": round(t_build, 1)},
+               "roofline": roofline, "step_roofline_frac": step_frac, "a_step_bytes": a_step,
+               "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+        print(json.dumps(out))
+    dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -133,7 +259,10 @@ def main():
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
 
-    # ---- build the case (every rank holds one slab-sized copy of the workload: weak scaling) ----
+    if world > 1:
+        return slab_main(a, pk, stream, rank, world, local_rank, warmup)
+
+    # ---- build the case ----
     t_build = time.perf_counter()
     case = pk.cases.DamBreak(pk.host, ndim=3, dp=a.dp, real_bytes=a.real, with_observer=True, device=local_rank,
                              stream=stream.cuda_stream)
