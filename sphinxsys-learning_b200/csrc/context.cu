@@ -235,6 +235,10 @@ void sphb200_ctx_destroy(sphb200_ctx *ctx)
             cudaFree(l.slice_w);
             cudaFree(l.slice_off);
             cudaFree(l.list);
+            cudaFree(l.uni.count);
+            cudaFree(l.uni.slice_w);
+            cudaFree(l.uni.slice_off);
+            cudaFree(l.uni.list);
         }
         delete r;
     }

@@ -800,9 +800,52 @@ __global__ void __launch_bounds__(128)
         out[i * width + d] = double(acc[d] / (w + Tiny<R>::value));
 }
 
+} // namespace sphb
+#include "tile.cuh"
+namespace sphb
+{
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
+// The register-tiled kernels (tile.cuh) serve every non-periodic body; SPHB200_TILE=0 keeps the
+// list-per-particle kernels (A/B timing, and the periodic cases always use them).
+static bool tileEnabled()
+{
+    static int on = -1;
+    if (on < 0)
+    {
+        const char *e = getenv("SPHB200_TILE");
+        on = (e && e[0] == '0') ? 0 : 1;
+    }
+    return on == 1;
+}
+template <int D, class R>
+static bool tileUsable(sphb200_relation *inner, sphb200_relation *wall)
+{
+    if (!tileEnabled() || inner->body->P<D, R>().per.mask || !inner->lists[0].sorted)
+        return false;
+    if (wall)
+        for (auto &L : wall->lists)
+            if (!L.sorted)
+                return false;
+    return true;
+}
+template <int D, class R>
+static sphb200_status makeUContactP(sphb200_relation *wall, const ContactP<R> &cp, UContactP<R> &out)
+{
+    out.n = cp.n;
+    for (int t = 0; t < cp.n; ++t)
+    {
+        SPHB_TRY((ensureUnion<TileG<R>::value>(wall->ctx, wall->body, wall->lists[size_t(t)])));
+        out.t[t].u = ulistOf(wall->lists[size_t(t)].uni);
+        out.t[t].xV = cp.t[t].xV;
+        out.t[t].vel = cp.t[t].vel;
+        out.t[t].acc = cp.t[t].acc;
+        out.t[t].nrm = cp.t[t].nrm;
+    }
+    return SPHB200_OK;
+}
+
 template <class R>
 static ListP<R> listOf(const NeighborList &L)
 {
@@ -966,7 +1009,18 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
         SPHB_TRY(reduceReset(ctx, 0, false));
         auto *slot = static_cast<unsigned long long *>(ctx->reduce_dev.p);
         const int grid = groupGrid(b->own_begin, b->own_end, 128);
-        if (P.per.mask)
+        if (tileUsable<D, R>(inner, wall))
+        {
+            constexpr int G = TileG<R>::value;
+            SPHB_TRY((ensureUnion<G>(ctx, b, inner->lists[0])));
+            UContactP<R> uw;
+            SPHB_TRY((makeUContactP<D, R>(wall, wp, uw)));
+            const UnionList &U = inner->lists[0].uni;
+            k_first_half_tile<D, R, G><<<gridFor(U.n_groups, 128), 128, 0, ctx->stream>>>(
+                U.base, b->own_begin, b->own_end, U.n_groups, rec_a, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern),
+                makeTileKernelP<R>(kern_w), fl, dt, rho, mass, fprior, force, drho, vel, slot);
+        }
+        else if (P.per.mask)
             k_first_half<D, R, true><<<grid, 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_a, rec_b, listOf<R>(inner->lists[0]), wp,
                                                                   P.kern, kern_w, P.per, fl, dt, rho, mass, fprior, force, drho, vel, slot);
         else
@@ -1017,7 +1071,18 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
     }
     if (b->own_begin > 0 || b->own_end < b->n)
         b->rec_b_valid = false; // one use only: the next 2nd half needs the halo records refreshed again
-    if (P.per.mask)
+    if (tileUsable<D, R>(inner, wall))
+    {
+        constexpr int G = TileG<R>::value;
+        SPHB_TRY((ensureUnion<G>(ctx, b, inner->lists[0])));
+        UContactP<R> uw;
+        SPHB_TRY((makeUContactP<D, R>(wall, wp, uw)));
+        const UnionList &U = inner->lists[0].uni;
+        k_second_half_tile<D, R, G><<<gridFor(U.n_groups, 128), 128, 0, ctx->stream>>>(
+            U.base, b->own_begin, b->own_end, U.n_groups, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern), makeTileKernelP<R>(kern_w), fl,
+            R(dt_), pos, rho, drho, force);
+    }
+    else if (P.per.mask)
         k_second_half<D, R, true><<<groupGrid(b->own_begin, b->own_end, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_b, listOf<R>(inner->lists[0]), wp,
                                                                              P.kern, kern_w, P.per, fl, R(dt_), pos, rho, drho, force);
     else

@@ -128,8 +128,28 @@ constexpr int kS = SPHB_LANES; // lanes per particle in the pair-sum kernels
 constexpr int kP = 32 / kS;    // particles per slice
 static_assert(kS == 1 || kS == 2 || kS == 4 || kS == 8, "SPHB_LANES must be 1, 2, 4 or 8");
 
+// Union list of a group of G consecutive source particles (tile.cuh): the ascending merge of the members'
+// neighbour lists, SELL-32 over groups (entry k of group g at list[32*(slice_off[g/32] + k) + g%32]).
+// One thread of the register-tiled pair kernels owns a group: every gathered neighbour record is used for
+// all G members (masked by the cut-off test), which divides the L1 gather traffic per useful pair.
+struct UnionList
+{
+    u32 *count = nullptr;     // [n_groups]
+    u32 *slice_w = nullptr;   // [n_groups/32]
+    u32 *slice_off = nullptr; // [n_groups/32 + 1]
+    u32 *list = nullptr;
+    size_t cap_groups = 0, cap_entries = 0;
+    int G = 0;
+    int64_t base = 0, n_groups = 0, own_begin = -1, own_end = -1;
+    u64 total_entries = 0;
+    uint64_t build_id = 0; // NeighborList::build_id this union was merged from
+};
+
 struct NeighborList
 {
+    UnionList uni;
+    uint64_t build_id = 0;    // bumped by every relation_update
+    bool sorted = false;      // every particle's entries ascend (non-periodic searches)
     u32 *count = nullptr;     // [n_src]
     u32 *slice_w = nullptr;   // [n_slices]  max over the slice of ceil(count/kS)
     u32 *slice_off = nullptr; // [n_slices+1] exclusive scan of slice_w (units of 32 entries)

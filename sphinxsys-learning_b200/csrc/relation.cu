@@ -479,6 +479,7 @@ static sphb200_status relationUpdate(sphb200_relation *r)
         if (n == 0)
         {
             r->target_stamp[k] = tgt->config_stamp;
+            L.build_id++;
             continue;
         }
         auto *xs = static_cast<const typename Real4<R>::type *>(src->xV.p);
@@ -543,6 +544,8 @@ static sphb200_status relationUpdate(sphb200_relation *r)
             k_search<D, R, true><<<gridFor(n, 128), 128, 0, st>>>(n, xs, xt, off, sp, L.count, L.slice_w, L.slice_off, L.list);
         SPHB_LAUNCH_CHECK(ctx);
         r->target_stamp[k] = tgt->config_stamp;
+        L.build_id++;
+        L.sorted = Pt.per.mask == 0; // both non-periodic searches emit ascending j per particle
     }
     r->source_stamp = src->config_stamp;
     r->valid = true;
