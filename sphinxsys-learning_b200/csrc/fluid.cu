@@ -807,22 +807,27 @@ namespace sphb
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
-// The register-tiled kernels (tile.cuh) serve every non-periodic body; SPHB200_TILE=0 keeps the
-// list-per-particle kernels (A/B timing, and the periodic cases always use them).
-static bool tileEnabled()
+// The register-tiled kernels (tile.cuh) serve non-periodic fp64 bodies by default: measured on B200 at
+// 20 M particles K2/K3 take 9.68/9.47 ms tiled against 11.36/10.56 ms per-particle in fp64, but 4.41/4.20
+// against 4.37/4.07 ms in fp32 (issue-bound there, the masked pairs cost more than the saved gathers).
+// SPHB200_TILE=0 / 1 forces the choice for both precisions (A/B timing and the parity tests of both paths).
+static int tileMode()
 {
-    static int on = -1;
-    if (on < 0)
+    static int mode = -2;
+    if (mode == -2)
     {
         const char *e = getenv("SPHB200_TILE");
-        on = (e && e[0] == '0') ? 0 : 1;
+        mode = !e ? -1 : (e[0] == '0' ? 0 : 1);
     }
-    return on == 1;
+    return mode;
 }
 template <int D, class R>
 static bool tileUsable(sphb200_relation *inner, sphb200_relation *wall)
 {
-    if (!tileEnabled() || inner->body->P<D, R>().per.mask || !inner->lists[0].sorted)
+    const int mode = inner->ctx->pair_kernel == -2 ? tileMode() : inner->ctx->pair_kernel;
+    if (mode == 0 || (mode < 0 && sizeof(R) == 4))
+        return false;
+    if (inner->body->P<D, R>().per.mask || !inner->lists[0].sorted)
         return false;
     if (wall)
         for (auto &L : wall->lists)
@@ -1266,6 +1271,13 @@ static sphb200_status observe(sphb200_relation *contact, const char *name, int w
 
 extern "C"
 {
+sphb200_status sphb200_ctx_set_pair_kernel(sphb200_ctx *ctx, int mode)
+{
+    if (!ctx || mode < -1 || mode > 1)
+        return SPHB200_ERR_INVALID;
+    ctx->pair_kernel = mode;
+    return SPHB200_OK;
+}
 sphb200_status sphb200_density_summation(sphb200_relation *inner, sphb200_relation *contact, int free_surface)
 {
     if (!inner)

@@ -207,6 +207,7 @@ struct sphb200_ctx
     bool owns_stream = true;
     std::string error;
     int64_t launches = 0;
+    int pair_kernel = -2; // -2: process default (env SPHB200_TILE), -1 auto, 0 per-particle lists, 1 group-tiled
     std::vector<sphb200_body *> bodies;
     std::vector<sphb200_relation *> relations;
     sphb::DevBuf scratch_a, scratch_b, scan_tmp, reduce_dev, mask_buf;

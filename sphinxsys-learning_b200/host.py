@@ -62,6 +62,10 @@ class SPHSystem:
         except Exception:
             pass
 
+    def set_pair_kernel(self, mode):
+        """-1 automatic, 0 list-per-particle, 1 group-tiled (include/sphb200.h)"""
+        self.check(self.lib.sphb200_ctx_set_pair_kernel(self.h, int(mode)))
+
     def synchronize(self):
         self.check(self.lib.sphb200_ctx_synchronize(self.h))
 

@@ -195,6 +195,41 @@ def test_fluid_dynamics_single_calls(pk, gpu, oracle, ndim, dp, real_bytes):
     assert np.allclose(pg, po, rtol=tol, atol=tol)
 
 
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("ndim,dp,real_bytes", [(3, 0.05, 8), (3, 0.05, 4), (2, 0.025, 8), (2, 0.025, 4)])
+def test_both_pair_kernel_families_match_oracle(pk, gpu, oracle, ndim, dp, real_bytes, mode):
+    """sphb200_ctx_set_pair_kernel: the list-per-particle kernels (0) and the group-tiled kernels on union
+    lists (1) must both reproduce the oracle's 1st/2nd half, with wall + Riemann and inner-only"""
+    tol = FP_TOL[real_bytes]
+    g, o = both(pk, gpu, oracle, pk.cases.DamBreak, ndim=ndim, dp=dp, real_bytes=real_bytes)
+    g.sys.set_pair_kernel(mode)
+    for c in (g, o):
+        jitter(c.water, 0.2)
+        c.water.update_cell_list()
+        c.update_configuration()
+    state = seeded_state(g)
+    dt = 0.3 * o.sys.acoustic_dt(o.water)
+    for wall, riemann in ((True, True), (False, False), (True, False)):
+        for c in (g, o):
+            load_state(c, state)
+            c.sys.integration_1st_half(c.inner, c.wall_contact if wall else None, riemann, dt)
+        assert g.sys.acoustic_dt(g.water) == pytest.approx(o.sys.acoustic_dt(o.water), rel=tol)
+        for name in FLUID_FIELDS:
+            assert rel_l2(field(g.water, name), field(o.water, name)) < tol, (name, wall, riemann)
+        for c in (g, o):
+            c.sys.integration_2nd_half(c.inner, c.wall_contact if wall else None, riemann, dt)
+        for name in FLUID_FIELDS:
+            assert rel_l2(field(g.water, name), field(o.water, name)) < tol, (name, wall, riemann)
+    # a few whole advection steps (re-sort + relation rebuild between them: the union lists follow)
+    for c in (g, o):
+        load_state(c, state)
+    for s in range(4):
+        rg, ro = g.advection_step(sort_interval=2), o.advection_step(sort_interval=2)
+        assert rg[1] == ro[1]
+    for name in ("Density", "Pressure", "Velocity", "Position"):
+        assert rel_l2(field(g.water, name), field(o.water, name)) < tol * 10, name
+
+
 @pytest.mark.parametrize("ndim,dp,steps", [(2, 0.025, 30), (3, 0.05, 12)])
 def test_dambreak_steps_match_oracle(pk, gpu, oracle, ndim, dp, steps):
     """whole advection steps (density summation, acoustic loop, sort, cell list, relations) in lockstep"""

@@ -83,12 +83,15 @@ def test_dist_comm_protocol_over_gloo(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n_slabs,real_bytes", [(2, 8), (3, 8), (2, 4)])
-def test_slabs_equal_single_gpu(pk, gpu, slab, n_slabs, real_bytes):
+@pytest.mark.parametrize("n_slabs,real_bytes,pair_kernel", [(2, 8, -1), (3, 8, 0), (2, 4, -1), (3, 4, 1)])
+def test_slabs_equal_single_gpu(pk, gpu, slab, n_slabs, real_bytes, pair_kernel):
     """N slabs emulated in one process (LocalComm) against the undecomposed run"""
     dp, steps = 0.05, 6
     one = pk.cases.DamBreak(gpu, ndim=3, dp=dp, real_bytes=real_bytes, with_observer=False)
     many = slab.SlabDamBreak(gpu, slab.LocalComm(n_slabs), dp=dp, real_bytes=real_bytes)
+    one.sys.set_pair_kernel(pair_kernel)
+    for P in many.parts:
+        P.case.sys.set_pair_kernel(pair_kernel)
     assert many.n_fluid() == one.water.n
     assert sum(1 for P in many.parts if P.oe > P.ob) == n_slabs  # every slab owns fluid
     # global ids of the single run, from its initial lattice
