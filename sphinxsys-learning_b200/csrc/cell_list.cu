@@ -299,6 +299,48 @@ __global__ void __launch_bounds__(256) k_cell_keys(const R *__restrict__ pos, in
     morton[i] = (long long)m;
 }
 
+// min / max of Vol over the whole body as u64 bit patterns of non-negative doubles (order preserving)
+template <class R>
+__global__ void __launch_bounds__(256) k_vol_minmax(const typename Real4<R>::type *__restrict__ xV, int64_t n,
+                                                    unsigned long long *__restrict__ mm)
+{
+    double lo = 1.7976931348623157e308, hi = 0.0;
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x)
+    {
+        const double v = double(reinterpret_cast<const R *>(xV + i)[3]);
+        lo = fmin(lo, v);
+        hi = fmax(hi, v);
+    }
+    lo = warpMin<double>(lo);
+    hi = warpMax<double>(hi);
+    if ((threadIdx.x & 31) == 0)
+    {
+        atomicMinNonNeg(mm, lo);
+        atomicMaxNonNeg(mm + 1, hi);
+    }
+}
+
+template <int D, class R>
+sphb200_status refreshVolRange(sphb200_body *b)
+{
+    sphb200_ctx *ctx = b->ctx;
+    SPHB_CUDA(ctx, b->vol_mm.ensure(16));
+    // min slot = all ones (above every finite pattern), max slot = 0: an empty body reads as "not uniform"
+    SPHB_CUDA(ctx, cudaMemsetAsync(b->vol_mm.p, 0xff, 8, ctx->stream));
+    SPHB_CUDA(ctx, cudaMemsetAsync(static_cast<char *>(b->vol_mm.p) + 8, 0, 8, ctx->stream));
+    if (b->n > 0)
+    {
+        k_vol_minmax<R><<<148 * 2, 256, 0, ctx->stream>>>(static_cast<const typename Real4<R>::type *>(b->xV.p), b->n,
+                                                       static_cast<unsigned long long *>(b->vol_mm.p));
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    return SPHB200_OK;
+}
+template sphb200_status refreshVolRange<2, float>(sphb200_body *);
+template sphb200_status refreshVolRange<2, double>(sphb200_body *);
+template sphb200_status refreshVolRange<3, float>(sphb200_body *);
+template sphb200_status refreshVolRange<3, double>(sphb200_body *);
+
 template <int D, class R>
 sphb200_status ensurePacked(sphb200_body *b)
 {
@@ -315,7 +357,7 @@ sphb200_status ensurePacked(sphb200_body *b)
     SPHB_LAUNCH_CHECK(ctx);
     b->xV_vol_dirty = false;
     b->rec_b_valid = false;
-    return SPHB200_OK;
+    return refreshVolRange<D, R>(b);
 }
 template sphb200_status ensurePacked<2, float>(sphb200_body *);
 template sphb200_status ensurePacked<2, double>(sphb200_body *);
@@ -383,6 +425,7 @@ static sphb200_status cellListUpdate(sphb200_body *b)
     b->xV_vol_dirty = false;
     b->rec_b_valid = false;
     b->config_stamp++;
+    SPHB_TRY((refreshVolRange<D, R>(b)));
     return updateOwnedRange(b);
 }
 

@@ -185,8 +185,8 @@ __global__ void __launch_bounds__(128)
 
 // ---------------------------------------------------------------------------------------------
 // Acoustic sub-step.  Neighbour state is gathered from packed records (internal.cuh Rec8):
-//   K1 k_first_half_init : rho, p, x update; writes rec_a[i] = {x_cfg, Vol | p_new, v}
-//   K2 k_first_half      : gathers rec_a[j] (x_cfg, Vol, p); writes rec_b[i] = {x_cfg, Vol | p, v_new}
+//   K1 k_first_half_init : rho, p, x update; writes rec_a[i] = {x_cfg, p_new | Vol, v}
+//   K2 k_first_half      : gathers rec_a[j] (x_cfg, p, Vol); writes rec_b[i] = {x_cfg, p | Vol, v_new}
 //   K3 k_second_half     : gathers rec_b[j] (x_cfg, Vol, v)
 // rec_a / rec_b ping-pong so that no kernel reads a line another thread of the same launch writes.
 // ---------------------------------------------------------------------------------------------
@@ -197,8 +197,8 @@ __device__ __forceinline__ void recSplit(const R *rec, R *x, R &V, R &p, R *v)
     x[1] = rec[1];
     if (D == 3)
         x[D - 1] = rec[2];
-    V = rec[3];
-    p = rec[4];
+    p = rec[3];
+    V = rec[4];
     v[0] = rec[5];
     v[1] = rec[6];
     if (D == 3)
@@ -210,8 +210,8 @@ __device__ __forceinline__ void recJoin(R *rec, const R *x, R V, R p, const R *v
     rec[0] = x[0];
     rec[1] = x[1];
     rec[2] = D == 3 ? x[D - 1] : R(0);
-    rec[3] = V;
-    rec[4] = p;
+    rec[3] = p;
+    rec[4] = V;
     rec[5] = v[0];
     rec[6] = v[1];
     rec[7] = D == 3 ? v[D - 1] : R(0);
@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(128, sizeof(R) == 8 ? SPHB_MINB_F64 : SPHB_MIN
             xj[1] = rj[1];
             if (D == 3)
                 xj[D - 1] = rj[2];
-            const R Vj = rj[3], pj = rj[4];
+            const R pj = rj[3], Vj = rj[4];
             if (PER)
                 periodicImage<D, R>(xi, xj, per);
             Pair<D, R> g;
@@ -949,7 +949,10 @@ static sphb200_status densitySummation(sphb200_relation *inner, sphb200_relation
         rho, vol, xV, free_surface);
     SPHB_LAUNCH_CHECK(ctx);
     if (!free_surface)
+    {
         b->rec_b_valid = false; // Vol changed
+        SPHB_TRY((refreshVolRange<D, R>(b)));
+    }
     return SPHB200_OK;
 }
 
@@ -1023,7 +1026,8 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
             const UnionList &U = inner->lists[0].uni;
             k_first_half_tile<D, R, G><<<gridFor(U.n_groups, 128), 128, 0, ctx->stream>>>(
                 U.base, b->own_begin, b->own_end, U.n_groups, rec_a, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern),
-                makeTileKernelP<R>(kern_w), fl, dt, rho, mass, fprior, force, drho, vel, slot);
+                makeTileKernelP<R>(kern_w), fl, dt, rho, mass, fprior, force, drho, vel, slot,
+                static_cast<const unsigned long long *>(b->vol_mm.p));
         }
         else if (P.per.mask)
             k_first_half<D, R, true><<<grid, 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_a, rec_b, listOf<R>(inner->lists[0]), wp,

@@ -41,8 +41,11 @@ struct Real4<double>
 };
 
 // Packed per-particle record of the acoustic sub-step kernels: one aligned 8-Real line
-// {x, y, z, Vol | p, vx, vy, vz} (32 B in fp32 = one L2 sector, 64 B in fp64 = two), fetched per
-// neighbour with 256-bit loads.  x and Vol are the values frozen at configuration time.
+// {x, y, z, p | Vol, vx, vy, vz} (32 B in fp32 = one L2 sector, 64 B in fp64 = two), fetched per
+// neighbour with 256-bit loads.  x and Vol are the values frozen at configuration time.  The first half
+// is all the 1st-half pair sum needs when every particle of the body has the same Vol (the usual state of a
+// free-surface WCSPH body: body.vol_mm holds min/max of Vol, the kernel folds the constant in) - the L1 data
+// pipe moves one 32-byte sector per cycle per SM for scattered gathers, so halving the sectors halves its time.
 template <class R>
 struct alignas(8 * sizeof(R)) Rec8
 {
@@ -237,6 +240,7 @@ struct sphb200_body
     sphb::DevBuf cell_count, cell_offset;            // u32[cells+1]
     sphb::DevBuf xV;                                 // Real4[n]: frozen position + Vol
     sphb::DevBuf rec_a, rec_b;                       // Rec8[n]: {xV | p, v} before / after the 1st-half update
+    sphb::DevBuf vol_mm;                             // u64[2]: bit patterns of min / max of xV[].w (Vol), see refreshVolRange
     bool rec_b_valid = false;                        // rec_b matches xV, Pressure and Velocity
     sphb::DevBuf tmp_var;                            // permutation double buffer
     int64_t n_cells = 0;
@@ -326,6 +330,10 @@ sphb200_status exclusiveScanU32(sphb200_ctx *ctx, const u32 *in, u32 *out, int64
 template <int D, class R>
 sphb200_status ensurePacked(sphb200_body *b);
 
+// min / max of the packed Vol into body.vol_mm (device side only; the 1st-half kernels read it)
+template <int D, class R>
+sphb200_status refreshVolRange(sphb200_body *b);
+
 // slab.cu: owned pages → owned particle range, after a cell_list_update
 sphb200_status updateOwnedRange(sphb200_body *b);
 
@@ -394,13 +402,16 @@ __device__ __forceinline__ void ldRec(const Rec8<double> *r, u32 j, double *v)
     ld256(r[j].a, v);
     ld256(r[j].a + 4, v + 4);
 }
-// {x, y, z, Vol, p}: fp32 gets the whole line anyway, fp64 adds one 8-byte load from the second sector
+// {x, y, z, p, Vol}: fp32 gets the whole line anyway, fp64 adds one 8-byte load from the second sector
 __device__ __forceinline__ void ldRecXVp(const Rec8<float> *r, u32 j, float *v) { ld256(r[j].a, v); }
 __device__ __forceinline__ void ldRecXVp(const Rec8<double> *r, u32 j, double *v)
 {
     ld256(r[j].a, v);
     v[4] = __ldg(r[j].a + 4);
 }
+// {x, y, z, p} only (uniform-Vol bodies): one sector in either precision
+__device__ __forceinline__ void ldRecXp(const Rec8<float> *r, u32 j, float *v) { ld256(r[j].a, v); }
+__device__ __forceinline__ void ldRecXp(const Rec8<double> *r, u32 j, double *v) { ld256(r[j].a, v); }
 __device__ __forceinline__ void stRec(Rec8<float> *r, int64_t i, const float *v) { st256(r[i].a, v); }
 __device__ __forceinline__ void stRec(Rec8<double> *r, int64_t i, const double *v)
 {

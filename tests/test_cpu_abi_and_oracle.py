@@ -31,6 +31,19 @@ def test_no_device_is_a_loud_error(pk):
     assert e.value.status == pk.capi.ERR_NO_DEVICE
 
 
+def test_cpp_adapter_main_builds_and_fails_loudly_without_a_gpu(pk):
+    """include/sphb200_adapter.hpp + examples/dambreak_3d.cpp (the reference's main on the C++ host side)"""
+    import subprocess
+    import torch
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "examples")])
+    exe = os.path.join(ROOT, "examples", "dambreak_3d")
+    assert os.path.exists(exe)
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present: the run itself is covered by the gpu tests")
+    r = subprocess.run([exe, "0.1", "1"], capture_output=True, text=True)
+    assert r.returncode == 1 and "no CUDA device" in r.stderr
+
+
 def test_product_package_never_touches_the_oracle():
     pkg = os.path.join(ROOT, "sphinxsys-learning_b200")
     for dirpath, _, files in os.walk(pkg):

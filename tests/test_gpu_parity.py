@@ -324,3 +324,27 @@ def test_large_lattice_properties(pk, gpu):
     for _ in range(2):
         c.advection_step()
     assert np.isfinite(c.mechanical_energy())
+
+
+@pytest.mark.gpu
+def test_cpp_adapter_main_equals_python_host(pk, gpu):
+    """examples/dambreak_3d (C++ adapter, the reference's main loop) and the Python harness drive the same
+    library on the same lattice: identical Dt / sub-step sequence, energy and probe pressures"""
+    import os
+    import re
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.check_call(["make", "-s", "-C", os.path.join(root, "examples")])
+    steps = 6
+    out = subprocess.run([os.path.join(root, "examples", "dambreak_3d"), "0.05", str(steps)], capture_output=True, text=True, check=True).stdout
+    seq = [(float(m.group(1)), int(m.group(2))) for m in re.finditer(r"Dt=(\S+) sub_steps=(\d+)", out)]
+    energy = float(re.search(r"energy=(\S+)", out).group(1))
+    probes = [float(x) for x in re.search(r"probes=(.*)", out).group(1).split()]
+    assert int(re.search(r"fluid=(\d+)", out).group(1)) == 8000 and int(re.search(r"launches=(\d+)", out).group(1)) > 0
+    c = pk.cases.DamBreak(gpu, ndim=3, dp=0.05, real_bytes=8)
+    ref = [c.advection_step(sort_interval=0) for _ in range(steps)]
+    assert len(seq) == steps
+    for (Dt, k), (Dt_ref, k_ref) in zip(seq, ref):
+        assert k == k_ref and Dt == pytest.approx(Dt_ref, rel=1e-13)
+    assert energy == pytest.approx(c.mechanical_energy(), rel=1e-12)
+    assert np.allclose(probes, c.probe_pressure(), rtol=1e-9, atol=1e-12)
