@@ -317,8 +317,17 @@ def main():
     k_ms = k0.elapsed_time(k1) / reps
     peak, peak_src = peaks()
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_second_half (Integration2ndHalf inner+wall, fused init/update)",
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    traffic = None
+    try:  # DRAM bytes of this kernel at this size from the committed ncu --set full capture (profiles/traffic.json)
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+            tj = json.load(fh)
+        key = f"k_second_half_tile<3,double,2>@{n_f}"
+        if R == 8 and key in tj:
+            traffic = tj[key]["dram_bytes_per_launch"]
+    except Exception:
+        traffic = None
+    roofline = {"bound": "hbm", "kernel": "Integration2ndHalf inner+wall, fused init/update (k_second_half_tile in fp64, k_second_half in fp32)",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "peak_source": peak_src, "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg_bytes,
                 "pairs_per_particle": (pairs_in + pairs_w) / n_f}
     a_step = 56 * R + 2 * 4 * (pairs_in + pairs_w) / n_f  # SURVEY §8d A_step: 448/224 B fields + 2 list reads

@@ -341,7 +341,10 @@ __global__ void __launch_bounds__(128) k_search_mask(int64_t n_src, const typena
 // Rows of the sliced-ELL list are assembled in shared memory (each thread drops its particle's indices
 // into its own columns) and written out as whole 128-byte rows.  kExpandRows rows per slice are staged;
 // the rare particle with more than kExpandRows*kS neighbours writes its tail straight to global memory.
-constexpr int kExpandRows = 64;
+#ifndef SPHB_EXPAND_ROWS
+#define SPHB_EXPAND_ROWS 44
+#endif
+constexpr int kExpandRows = SPHB_EXPAND_ROWS;
 constexpr int kExpandBlock = 128;
 constexpr size_t kExpandSmem = size_t(kExpandBlock / 32) * kS * kExpandRows * 32 * sizeof(u32);
 
