@@ -315,6 +315,13 @@ class Relation:
         """SPHRelation::updateConfiguration"""
         self.sys.check(self.lib.sphb200_relation_update(self.h))
 
+    def neighbor_counts(self, k=0):
+        """counts[n] only (no index list): cheap at full size"""
+        total = C.c_int64()
+        counts = np.zeros(self.body.n, dtype=np.int32)
+        self.sys.check(self.lib.sphb200_relation_neighbors(self.h, k, counts.ctypes.data_as(C.POINTER(C.c_int32)), None, C.byref(total)))
+        return counts, int(total.value)
+
     def neighbors(self, k=0):
         """(counts[n], flat j in list order) of target k - parity/debug"""
         n = self.body.n

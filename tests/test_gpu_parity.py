@@ -327,6 +327,43 @@ def test_large_lattice_properties(pk, gpu):
 
 
 @pytest.mark.gpu
+def test_full_size_dambreak_properties(pk, gpu):
+    """BASELINE.json configs[2] at its full size (20 123 648 fluid particles): size-independent properties, and
+    the two pair-kernel families against each other on a non-trivial state"""
+    c = pk.cases.DamBreak(gpu, ndim=3, dp=1.0 / 272.0, real_bytes=8, with_observer=False)
+    w = c.water
+    assert w.n == 544 * 272 * 136 == 20123648
+    lin, _ = w.cell_keys()
+    assert np.all(np.diff(lin) >= 0)
+    del lin
+    counts, total = c.inner.neighbor_counts()
+    assert counts.max() == 80 and total == int(counts.sum(dtype=np.int64)) and total % 2 == 0
+    interior = counts == 80
+    assert interior.mean() > 0.9
+    c.sys.density_summation(c.inner, c.wall_contact, True)
+    assert np.allclose(w.get("DensitySummation")[interior], 1.0, rtol=0, atol=1e-12)
+    e0 = c.mechanical_energy()
+    assert e0 == pytest.approx(0.5, rel=1e-12)  # rho0 * LL*LH*LW * g * LH/2
+    for _ in range(2):
+        c.advection_step()
+    assert c.mechanical_energy() == pytest.approx(e0, rel=1e-5)
+    assert w.get("Mass").sum() == pytest.approx(1.0, rel=1e-12)
+    # list-per-particle kernels vs group-tiled kernels from the same (moving) state: same sums, other rounding
+    names = ["Density", "Pressure", "Velocity", "Position", "Force", "DensityChangeRate"]
+    state = {nm: w.get(nm) for nm in names}
+    dt = c.dt
+    out = {}
+    for mode in (0, 1):
+        c.sys.set_pair_kernel(mode)
+        for nm, v in state.items():
+            w.set(nm, v)
+        c.acoustic_substep(dt)
+        out[mode] = {nm: w.get(nm) for nm in ("DensityChangeRate", "Force", "Velocity", "Density")}
+    for nm in out[0]:
+        assert rel_l2(out[1][nm], out[0][nm]) < 1e-10, nm
+
+
+@pytest.mark.gpu
 def test_cpp_adapter_main_equals_python_host(pk, gpu):
     """examples/dambreak_3d (C++ adapter, the reference's main loop) and the Python harness drive the same
     library on the same lattice: identical Dt / sub-step sequence, energy and probe pressures"""
