@@ -239,6 +239,10 @@ void sphb200_ctx_destroy(sphb200_ctx *ctx)
             cudaFree(l.uni.slice_w);
             cudaFree(l.uni.slice_off);
             cudaFree(l.uni.list);
+            cudaFree(l.uni_wide.count);
+            cudaFree(l.uni_wide.slice_w);
+            cudaFree(l.uni_wide.slice_off);
+            cudaFree(l.uni_wide.list);
         }
         delete r;
     }

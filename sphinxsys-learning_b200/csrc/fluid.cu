@@ -836,13 +836,18 @@ static bool tileUsable(sphb200_relation *inner, sphb200_relation *wall)
     return true;
 }
 template <int D, class R>
-static sphb200_status makeUContactP(sphb200_relation *wall, const ContactP<R> &cp, UContactP<R> &out)
+static sphb200_status makeUContactP(sphb200_relation *wall, const ContactP<R> &cp, UContactP<R> &out, bool wide)
 {
     out.n = cp.n;
     for (int t = 0; t < cp.n; ++t)
     {
-        SPHB_TRY((ensureUnion<TileG<R>::value>(wall->ctx, wall->body, wall->lists[size_t(t)])));
-        out.t[t].u = ulistOf(wall->lists[size_t(t)].uni);
+        NeighborList &L = wall->lists[size_t(t)];
+        wide = wide && kWideLanes > 1;
+        if (wide)
+            SPHB_TRY((ensureUnion<TileG<R>::value * kWideLanes>(wall->ctx, wall->body, L, L.uni_wide, kWideLanes)));
+        else
+            SPHB_TRY((ensureUnion<TileG<R>::value>(wall->ctx, wall->body, L, L.uni, 1)));
+        out.t[t].u = ulistOf(wide ? L.uni_wide : L.uni);
         out.t[t].xV = cp.t[t].xV;
         out.t[t].vel = cp.t[t].vel;
         out.t[t].acc = cp.t[t].acc;
@@ -1020,9 +1025,9 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
         if (tileUsable<D, R>(inner, wall))
         {
             constexpr int G = TileG<R>::value;
-            SPHB_TRY((ensureUnion<G>(ctx, b, inner->lists[0])));
+            SPHB_TRY((ensureUnion<G>(ctx, b, inner->lists[0], inner->lists[0].uni, 1)));
             UContactP<R> uw;
-            SPHB_TRY((makeUContactP<D, R>(wall, wp, uw)));
+            SPHB_TRY((makeUContactP<D, R>(wall, wp, uw, false)));
             const UnionList &U = inner->lists[0].uni;
             k_first_half_tile<D, R, G><<<gridFor(U.n_groups, 128), 128, 0, ctx->stream>>>(
                 U.base, b->own_begin, b->own_end, U.n_groups, rec_a, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern),
@@ -1083,12 +1088,14 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
     if (tileUsable<D, R>(inner, wall))
     {
         constexpr int G = TileG<R>::value;
-        SPHB_TRY((ensureUnion<G>(ctx, b, inner->lists[0])));
+        // 2nd half: kWideLanes adjacent threads share the union list of their 2 * kWideLanes particles
+        UnionList &U = kWideLanes > 1 ? inner->lists[0].uni_wide : inner->lists[0].uni;
+        SPHB_TRY((ensureUnion<G * kWideLanes>(ctx, b, inner->lists[0], U, kWideLanes)));
         UContactP<R> uw;
-        SPHB_TRY((makeUContactP<D, R>(wall, wp, uw)));
-        const UnionList &U = inner->lists[0].uni;
-        k_second_half_tile<D, R, G><<<gridFor(U.n_groups, 128), 128, 0, ctx->stream>>>(
-            U.base, b->own_begin, b->own_end, U.n_groups, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern), makeTileKernelP<R>(kern_w), fl,
+        SPHB_TRY((makeUContactP<D, R>(wall, wp, uw, true)));
+        const int64_t n_threads = (b->own_end - U.base + G - 1) / G;
+        k_second_half_tile<D, R, G, kWideLanes><<<gridFor(n_threads, 128), 128, 0, ctx->stream>>>(
+            U.base, b->own_begin, b->own_end, n_threads, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern), makeTileKernelP<R>(kern_w), fl,
             R(dt_), pos, rho, drho, force);
     }
     else if (P.per.mask)

@@ -142,7 +142,8 @@ struct UnionList
     u32 *slice_off = nullptr; // [n_groups/32 + 1]
     u32 *list = nullptr;
     size_t cap_groups = 0, cap_entries = 0;
-    int G = 0;
+    int G = 0;     // particles per union group
+    int lanes = 1; // threads of the pair kernel that walk one group's list together (a slice holds 32/lanes groups)
     int64_t base = 0, n_groups = 0, own_begin = -1, own_end = -1;
     u64 total_entries = 0;
     uint64_t build_id = 0; // NeighborList::build_id this union was merged from
@@ -150,7 +151,8 @@ struct UnionList
 
 struct NeighborList
 {
-    UnionList uni;
+    UnionList uni;      // groups of 2, one thread per group (1st half)
+    UnionList uni_wide; // groups of 4 shared by 2 adjacent threads of 2 members each (2nd half)
     uint64_t build_id = 0;    // bumped by every relation_update
     bool sorted = false;      // every particle's entries ascend (non-periodic searches)
     u32 *count = nullptr;     // [n_src]
