@@ -949,6 +949,16 @@ static sphb200_status densitySummation(sphb200_relation *inner, sphb200_relation
     SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
     SPHB_TRY(getVarPtr<R>(b, "VolumetricMeasure", 1, &vol, true));
     auto *xV = static_cast<typename Real4<R>::type *>(b->xV.p);
+    if (tileUsable<D, R>(inner, contact))
+    {
+        constexpr int G = TileG<R>::value;
+        SPHB_TRY((ensureUnion<G>(ctx, b, inner->lists[0], inner->lists[0].uni, 1)));
+        const UnionList &U = inner->lists[0].uni;
+        k_density_summation_tile<D, R, G><<<gridFor(U.n_groups, 128), 128, 0, ctx->stream>>>(
+            U.base, b->own_begin, b->own_end, U.n_groups, xV, ulistOf(U), ct, P.kern, kern_ct, R(b->rho0), R(1.0) / P.sigma0, mass, rho_sum,
+            rho, vol, xV, free_surface);
+    }
+    else
     k_density_summation<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
         b->own_begin, b->own_end, xV, listOf<R>(inner->lists[0]), ct, P.kern, kern_ct, P.per, R(b->rho0), R(1.0) / P.sigma0, mass, rho_sum,
         rho, vol, xV, free_surface);
