@@ -371,9 +371,11 @@ __device__ __forceinline__ R sqnormExact(const R *d)
 __device__ __forceinline__ float4 ldg4(const float4 *p) { return __ldg(p); }
 __device__ __forceinline__ double4 ldg4(const double4 *p)
 {
-    const double2 *q = reinterpret_cast<const double2 *>(p);
-    double2 a = __ldg(q), b = __ldg(q + 1);
-    return make_double4(a.x, a.y, b.x, b.y);
+    // one LDG.E.256 (the Real4 arrays are 32-byte aligned: cudaMalloc base, 32-byte elements) instead of two 128-bit
+    // loads: half the load instructions and L1 wavefronts per candidate / neighbour
+    double4 v;
+    asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v.x), "=d"(v.y), "=d"(v.z), "=d"(v.w) : "l"(p));
+    return v;
 }
 
 // 256-bit loads/stores of record halves (LDG.E.256 on sm_100a)
