@@ -180,10 +180,44 @@ __global__ void __launch_bounds__(256) k_scatter_perm(const u32 *__restrict__ ce
         perm[cell_offset[cell_of[i]] + rank[i]] = u32(i);
 }
 
-// order the entries of every cell by previous particle index: makes the sort stable and the whole
-// configuration (hence every floating-point sum order) reproducible run to run
-__global__ void __launch_bounds__(256) k_cell_order(const u32 *__restrict__ cell_offset, u32 *__restrict__ perm,
-                                                    int64_t n_cells)
+// In-cell order.  The reference's sort is unstable, so any order inside a cell is a legal outcome; this one is
+// geometric: a boustrophedon (snake) walk over 8^D sub-bins of the cell, previous index as the tie-break.
+// Consecutive particles are then nearest neighbours wherever the flow has taken them, which is what the
+// union lists of the register-tiled kernels (tile.cuh) want - the union of a close pair is smaller - and the
+// order is a function of the positions, reproducible run to run and between a slab run and the whole-domain run.
+template <int D, class R>
+__global__ void __launch_bounds__(256) k_cell_subkey(const R *__restrict__ pos, const u32 *__restrict__ perm,
+                                                     const u32 *__restrict__ cell_of, MeshP<D, R> mesh, int64_t n,
+                                                     unsigned long long *__restrict__ keys)
+{
+    int64_t k = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (k >= n)
+        return;
+    const u32 i = perm[k];
+    u32 c = cell_of[i]; // linear index: last axis fastest
+    int q[D];
+#pragma unroll
+    for (int a = D - 1; a >= 0; --a)
+    {
+        const u32 ca = c % u32(mesh.cells[a]);
+        c /= u32(mesh.cells[a]);
+        const R u = (pos[size_t(i) * D + a] - (mesh.lo[a] + R(ca) * mesh.spacing)) / mesh.spacing;
+        int v = int(u * R(8));
+        q[a] = v < 0 ? 0 : (v > 7 ? 7 : v); // clamped particles and rounding at the faces
+    }
+    u32 row = 0, key = 0;
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+    {
+        const int v = (row & 1u) ? 7 - q[a] : q[a];
+        key = key * 8u + u32(v);
+        row = row * 8u + u32(v);
+    }
+    keys[k] = ((unsigned long long)key << 32) | i;
+}
+
+__global__ void __launch_bounds__(256) k_cell_order(const u32 *__restrict__ cell_offset, unsigned long long *__restrict__ keys,
+                                                    u32 *__restrict__ perm, int64_t n_cells)
 {
     int64_t c = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (c >= n_cells)
@@ -191,15 +225,17 @@ __global__ void __launch_bounds__(256) k_cell_order(const u32 *__restrict__ cell
     u32 b = cell_offset[c], e = cell_offset[c + 1];
     for (u32 k = b + 1; k < e; ++k)
     {
-        u32 v = perm[k];
+        unsigned long long v = keys[k];
         u32 m = k;
-        while (m > b && perm[m - 1] > v)
+        while (m > b && keys[m - 1] > v)
         {
-            perm[m] = perm[m - 1];
+            keys[m] = keys[m - 1];
             --m;
         }
-        perm[m] = v;
+        keys[m] = v;
     }
+    for (u32 k = b; k < e; ++k)
+        perm[k] = u32(keys[k]);
 }
 
 // gather of one variable into the new order; T = element type, width elements per particle
@@ -397,7 +433,11 @@ static sphb200_status cellListUpdate(sphb200_body *b)
     {
         k_scatter_perm<<<gridFor(n, 256), 256, 0, st>>>(cell_of, rank, off, perm, n);
         SPHB_LAUNCH_CHECK(ctx);
-        k_cell_order<<<gridFor(nc, 256), 256, 0, st>>>(off, perm, nc);
+        SPHB_CUDA(ctx, ctx->subkey_buf.ensure(size_t(n) * 8));
+        auto *subkeys = static_cast<unsigned long long *>(ctx->subkey_buf.p);
+        k_cell_subkey<D, R><<<gridFor(n, 256), 256, 0, st>>>(pos, perm, cell_of, P.mesh, n, subkeys);
+        SPHB_LAUNCH_CHECK(ctx);
+        k_cell_order<<<gridFor(nc, 256), 256, 0, st>>>(off, subkeys, perm, nc);
         SPHB_LAUNCH_CHECK(ctx);
         // gather every registered variable into cell order (UpdateSortableVariables,
         // shared_ck/.../base_configuration_dynamics.h:74-128, one temp buffer swapped in)
