@@ -144,7 +144,9 @@ def slab_main(a, pk, stream, rank, world, local_rank, warmup):
     # ---- roofline of the dominant kernel on this rank's slab (owned particles as i) ----
     w = P.case.water
     owned = P.oe - P.ob
-    pairs = int(P.case.inner.neighbors()[0][P.ob:P.oe].sum()) + int(P.case.wall_contact.neighbors()[0][P.ob:P.oe].sum())
+    pairs = int(P.case.inner.neighbor_counts()[0][P.ob:P.oe].sum(dtype=np.int64)) + \
+        int(P.case.wall_contact.neighbor_counts()[0][P.ob:P.oe].sum(dtype=np.int64))
+    barrier()  # every rank times its kernel with the box otherwise quiet
     alg_bytes = owned * 20 * R + 4 * pairs
     reps = 5
     S = P.case.sys
@@ -255,6 +257,9 @@ def main():
         raise SystemExit("bench.py: no CUDA device - the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     if world > 1:
+        # keep stdout to the one JSON line: NCCL prints its version banner there at the VERSION/INFO levels
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     pk = importlib.import_module("sphinxsys-learning_b200")
     stream = torch.cuda.Stream()
@@ -299,9 +304,7 @@ def main():
     value = world * n_f * sub / (ms_max * 1e-3)
 
     # ---- roofline of the dominant kernel (Integration2ndHalf: one launch per call) ---------------
-    counts_in = case.inner.neighbors()[0]
-    counts_w = case.wall_contact.neighbors()[0]
-    pairs_in, pairs_w = int(counts_in.sum()), int(counts_w.sum())
+    pairs_in, pairs_w = case.inner.neighbor_counts()[1], case.wall_contact.neighbor_counts()[1]
     R = a.real
     fields_B = 20 * R  # K3 of SURVEY §8d: 160 B fp64 / 80 B fp32 per particle
     alg_bytes = n_f * fields_B + 4 * (pairs_in + pairs_w)
