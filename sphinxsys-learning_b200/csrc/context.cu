@@ -235,10 +235,13 @@ void sphb200_ctx_destroy(sphb200_ctx *ctx)
             cudaFree(l.slice_w);
             cudaFree(l.slice_off);
             cudaFree(l.list);
+            cudaFree(l.mask);
             cudaFree(l.uni.count);
             cudaFree(l.uni.slice_w);
             cudaFree(l.uni.slice_off);
             cudaFree(l.uni.list);
+            cudaFree(l.uni.queue);
+            cudaFree(l.uni_wide.queue);
             cudaFree(l.uni_wide.count);
             cudaFree(l.uni_wide.slice_w);
             cudaFree(l.uni_wide.slice_off);
@@ -254,7 +257,7 @@ void sphb200_ctx_destroy(sphb200_ctx *ctx)
             kv.second->alt.release();
         }
         for (DevBuf *d : {&b->original_id, &b->sorted_id, &b->cell_of, &b->rank_in_cell, &b->perm, &b->cell_count,
-                          &b->cell_offset, &b->xV, &b->tmp_var, &b->rec_a, &b->rec_b})
+                          &b->cell_offset, &b->xV, &b->tmp_var, &b->rec_a, &b->rec_b, &b->vol_mm, &b->xf})
             d->release();
         delete b;
     }

@@ -844,9 +844,9 @@ static sphb200_status makeUContactP(sphb200_relation *wall, const ContactP<R> &c
         NeighborList &L = wall->lists[size_t(t)];
         wide = wide && kWideLanes > 1;
         if (wide)
-            SPHB_TRY((ensureUnion<TileG<R>::value * kWideLanes>(wall->ctx, wall->body, L, L.uni_wide, kWideLanes)));
+            SPHB_TRY((ensureUnion<D, R, TileG<R>::value * kWideLanes>(wall, size_t(t), L.uni_wide, kWideLanes)));
         else
-            SPHB_TRY((ensureUnion<TileG<R>::value>(wall->ctx, wall->body, L, L.uni, 1)));
+            SPHB_TRY((ensureUnion<D, R, TileG<R>::value>(wall, size_t(t), L.uni, 1)));
         out.t[t].u = ulistOf(wide ? L.uni_wide : L.uni);
         out.t[t].xV = cp.t[t].xV;
         out.t[t].vel = cp.t[t].vel;
@@ -879,7 +879,7 @@ static sphb200_status checkRelation(sphb200_relation *r, bool want_inner, const 
     return SPHB200_OK;
 }
 
-// need: bit 0 mass, 1 velocity, 2 acceleration, 3 normal
+// need: bit 0 mass, 1 velocity, 2 acceleration, 3 normal, 4 the caller walks union lists: no per-particle index list
 template <int D, class R>
 static sphb200_status makeContactP(sphb200_relation *c, int need, ContactP<R> &out, KernelP<R> &kern_c)
 {
@@ -894,6 +894,8 @@ static sphb200_status makeContactP(sphb200_relation *c, int need, ContactP<R> &o
         sphb200_body *tb = c->targets[size_t(t)];
         SPHB_TRY((ensurePacked<D, R>(tb)));
         TargetP<R> &T = out.t[t];
+        if (!(need & 16))
+            SPHB_TRY(ensureList(c, size_t(t)));
         const NeighborList &L = c->lists[size_t(t)];
         T.count = L.count;
         T.slice_off = L.slice_off;
@@ -952,16 +954,19 @@ static sphb200_status densitySummation(sphb200_relation *inner, sphb200_relation
     if (tileUsable<D, R>(inner, contact))
     {
         constexpr int G = TileG<R>::value;
-        SPHB_TRY((ensureUnion<G>(ctx, b, inner->lists[0], inner->lists[0].uni, 1)));
+        SPHB_TRY((ensureUnion<D, R, G>(inner, 0, inner->lists[0].uni, 1)));
         const UnionList &U = inner->lists[0].uni;
         k_density_summation_tile<D, R, G><<<gridFor(U.n_groups, 128), 128, 0, ctx->stream>>>(
             U.base, b->own_begin, b->own_end, U.n_groups, xV, ulistOf(U), ct, P.kern, kern_ct, R(b->rho0), R(1.0) / P.sigma0, mass, rho_sum,
             rho, vol, xV, free_surface);
     }
     else
-    k_density_summation<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
+    {
+        SPHB_TRY(ensureList(inner, 0));
+        k_density_summation<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
         b->own_begin, b->own_end, xV, listOf<R>(inner->lists[0]), ct, P.kern, kern_ct, P.per, R(b->rho0), R(1.0) / P.sigma0, mass, rho_sum,
         rho, vol, xV, free_surface);
+    }
     SPHB_LAUNCH_CHECK(ctx);
     if (!free_surface)
     {
@@ -1028,14 +1033,17 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
     {
         ContactP<R> wp;
         KernelP<R> kern_w = P.kern;
-        SPHB_TRY((makeContactP<D, R>(wall, 4, wp, kern_w)));
+        const bool tiled = tileUsable<D, R>(inner, wall);
+        SPHB_TRY((makeContactP<D, R>(wall, tiled ? 4 | 16 : 4, wp, kern_w)));
+        if (!tiled)
+            SPHB_TRY(ensureList(inner, 0));
         SPHB_TRY(reduceReset(ctx, 0, false));
         auto *slot = static_cast<unsigned long long *>(ctx->reduce_dev.p);
         const int grid = groupGrid(b->own_begin, b->own_end, 128);
-        if (tileUsable<D, R>(inner, wall))
+        if (tiled)
         {
             constexpr int G = TileG<R>::value;
-            SPHB_TRY((ensureUnion<G>(ctx, b, inner->lists[0], inner->lists[0].uni, 1)));
+            SPHB_TRY((ensureUnion<D, R, G>(inner, 0, inner->lists[0].uni, 1)));
             UContactP<R> uw;
             SPHB_TRY((makeUContactP<D, R>(wall, wp, uw, false)));
             const UnionList &U = inner->lists[0].uni;
@@ -1076,7 +1084,10 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
     SPHB_TRY((ensureRecBuffers<D, R>(b)));
     ContactP<R> wp;
     KernelP<R> kern_w = P.kern;
-    SPHB_TRY((makeContactP<D, R>(wall, 2 | 8, wp, kern_w)));
+    const bool tiled = tileUsable<D, R>(inner, wall);
+    SPHB_TRY((makeContactP<D, R>(wall, tiled ? 2 | 8 | 16 : 2 | 8, wp, kern_w)));
+    if (!tiled)
+        SPHB_TRY(ensureList(inner, 0));
     FluidP<R> fl = makeFluidP<R>(b, P.h, riemann != 0);
     R *rho, *drho, *pos, *vel, *force, *p;
     SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
@@ -1095,12 +1106,12 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
     }
     if (b->own_begin > 0 || b->own_end < b->n)
         b->rec_b_valid = false; // one use only: the next 2nd half needs the halo records refreshed again
-    if (tileUsable<D, R>(inner, wall))
+    if (tiled)
     {
         constexpr int G = TileG<R>::value;
         // 2nd half: kWideLanes adjacent threads share the union list of their 2 * kWideLanes particles
         UnionList &U = kWideLanes > 1 ? inner->lists[0].uni_wide : inner->lists[0].uni;
-        SPHB_TRY((ensureUnion<G * kWideLanes>(ctx, b, inner->lists[0], U, kWideLanes)));
+        SPHB_TRY((ensureUnion<D, R, G * kWideLanes>(inner, 0, U, kWideLanes)));
         UContactP<R> uw;
         SPHB_TRY((makeUContactP<D, R>(wall, wp, uw, true)));
         const int64_t n_threads = (b->own_end - U.base + G - 1) / G;
@@ -1229,6 +1240,7 @@ static sphb200_status viscousForce(sphb200_relation *inner)
     SPHB_TRY(getVarPtr<R>(b, "ViscousForce", D, &vf));
     SPHB_TRY(getVarPtr<R>(b, "PreviousViscousForce", D, &prev, true));
     SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
+    SPHB_TRY(ensureList(inner, 0));
     k_viscous<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
         b->own_begin, b->own_end, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), P.kern, P.per,
         R(b->mu), P.h, vel, vf, prev, fprior);
@@ -1250,6 +1262,7 @@ static sphb200_status transportVelocity(sphb200_relation *inner, double coeffici
     SPHB_TRY(getVarPtr<R>(b, "KernelGradientIntegral", D, &kgi));
     SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos, true));
     R h2 = P.h * P.h;
+    SPHB_TRY(ensureList(inner, 0));
     k_transport_velocity<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
         b->own_begin, b->own_end, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), P.kern, P.per, h2,
         R(coefficient) * h2, kgi, pos);

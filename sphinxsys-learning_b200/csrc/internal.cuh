@@ -141,6 +141,7 @@ struct UnionList
     u32 *slice_w = nullptr;   // [n_groups/32]
     u32 *slice_off = nullptr; // [n_groups/32 + 1]
     u32 *list = nullptr;
+    u32 *queue = nullptr;     // [1 + n_groups] counter, then the groups whose members lie in different cells (k_union_mask)
     size_t cap_groups = 0, cap_entries = 0;
     int G = 0;     // particles per union group
     int lanes = 1; // threads of the pair kernel that walk one group's list together (a slice holds 32/lanes groups)
@@ -158,10 +159,14 @@ struct NeighborList
     u32 *count = nullptr;     // [n_src]
     u32 *slice_w = nullptr;   // [n_slices]  max over the slice of ceil(count/kS)
     u32 *slice_off = nullptr; // [n_slices+1] exclusive scan of slice_w (units of 32 entries)
-    u32 *list = nullptr;
+    u32 *list = nullptr;      // index list; filled on demand when the search left hit masks (ensureList)
     size_t cap_entries = 0, cap_src = 0;
     u64 total_entries = 0; // 32 * slice_off[n_slices]
     u64 total_pairs = 0;
+    u32 *mask = nullptr;   // hit bits of the masked search (relation.cu), kept until the next update
+    size_t cap_mask = 0;   // in words
+    bool has_mask = false; // this build's hits are in mask (fast search path)
+    bool expanded = false; // list holds this build's indices
 };
 
 // per-target device pointers handed to the interaction kernels
@@ -243,6 +248,8 @@ struct sphb200_body
     sphb::DevBuf xV;                                 // Real4[n]: frozen position + Vol
     sphb::DevBuf rec_a, rec_b;                       // Rec8[n]: {xV | p, v} before / after the 1st-half update
     sphb::DevBuf vol_mm;                             // u64[2]: bit patterns of min / max of xV[].w (Vol), see refreshVolRange
+    sphb::DevBuf xf;                                 // float4[n]: fp32 copy of (x - mesh.lo) for the search pre-filter (relation.cu)
+    uint64_t xf_stamp = ~uint64_t(0);                // config_stamp xf was made from
     bool rec_b_valid = false;                        // rec_b matches xV, Pressure and Velocity
     sphb::DevBuf tmp_var;                            // permutation double buffer
     int64_t n_cells = 0;
@@ -542,4 +549,50 @@ __device__ __forceinline__ R warpSum(R v)
     return v;
 }
 #endif // __CUDACC__
+// ---------------------------------------------------------------------------------------------
+// hit masks of the masked neighbour search (relation.cu: k_search_mask; readers: k_expand_mask, tile.cuh k_union_mask)
+// a particle's candidates are 3^(D-1) runs of consecutive target particles (the cells c-1..c+1 along the
+// fastest axis of one neighbouring column); kRunWords 32-bit words of hit bits per run
+// ---------------------------------------------------------------------------------------------
+constexpr int kRunWords = 4;
+template <int D>
+struct MaskLayout
+{
+    static constexpr int runs = D == 3 ? 9 : 3;
+    static constexpr int words = runs * kRunWords;
+};
+
+template <int D, class R>
+__device__ __forceinline__ void runRange(const int *c, int r, const MeshP<D, R> &mesh, const u32 *__restrict__ cell_offset,
+                                         u32 &b, u32 &e)
+{
+    // run r = (dx, dy) column offset in 3-D, dx in 2-D; empty when the column is outside the mesh
+    int cc[D];
+    bool inside = true;
+    if (D == 3)
+    {
+        cc[0] = c[0] + r / 3 - 1;
+        cc[1] = c[1] + r % 3 - 1;
+        inside = cc[0] >= 0 && cc[0] < mesh.cells[0] && cc[1] >= 0 && cc[1] < mesh.cells[1];
+    }
+    else
+    {
+        cc[0] = c[0] + r - 1;
+        inside = cc[0] >= 0 && cc[0] < mesh.cells[0];
+    }
+    if (!inside)
+    {
+        b = e = 0;
+        return;
+    }
+    int lo = max(c[D - 1] - 1, 0), hi = min(c[D - 1] + 1, mesh.cells[D - 1] - 1);
+    cc[D - 1] = lo;
+    u32 first = mesh.linear(cc);
+    b = __ldg(cell_offset + first);
+    e = __ldg(cell_offset + first + u32(hi - lo) + 1);
+}
+
+// fills lists[k].list from the hit masks if this build has not done so yet (relation.cu)
+sphb200_status ensureList(sphb200_relation *r, size_t k);
+
 } // namespace sphb

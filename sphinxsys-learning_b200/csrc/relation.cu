@@ -228,50 +228,49 @@ __global__ void __launch_bounds__(128) k_search(int64_t n_src, const typename Re
 // ~80 bit extractions.  A run longer than 32*kRunWords candidates raises the overflow flag and the host
 // falls back to the generic two-pass search.
 // ---------------------------------------------------------------------------------------------
-constexpr int kRunWords = 4;
-template <int D>
-struct MaskLayout
+// fp32 pre-filter of the fp64 search.  xf = float(x - mesh.lo); a candidate whose fp32 squared distance is
+// below pre.lo is a hit, above pre.hi a miss, and only what falls between (or is NaN: a particle outside
+// the mesh) takes the exact fp64 test, so the accepted set is bit-for-bit that of the exact test.  With
+// u = 2^-24, M = the largest |x - lo| of a particle inside the mesh (+ one cell) and d the true offset:
+// every fp32 coordinate is off by <= u M, a component of the fp32 offset by delta <= 2 u M + u |d_k|, and
+// the fp32 sum of squares by <= 2 sqrt(D) |d| delta + D delta^2 + 4 u |d|^2.  Near |d| = rc this is
+// tau0 = 2 sqrt(D) rc delta + D delta^2 + 4 u rc^2; the band is rc^2 -+ 4 tau0 (candidates lie within
+// 3.5 rc, where the error grows at most linearly in |d| while the margin |d|^2 - rc^2 grows faster).
+// The fp32 tests issue at twice the rate of the fp64 ones and read 16 instead of 32 bytes per candidate.
+struct PrefilterP
 {
-    static constexpr int runs = D == 3 ? 9 : 3;
-    static constexpr int words = runs * kRunWords;
+    float lo, hi;    // hit below lo, miss above hi
+    float limit[3];  // a coordinate outside [-spacing, limit] is stored as NaN
 };
-
 template <int D, class R>
-__device__ __forceinline__ void runRange(const int *c, int r, const MeshP<D, R> &mesh, const u32 *__restrict__ cell_offset,
-                                         u32 &b, u32 &e)
+__global__ void __launch_bounds__(256)
+    k_make_xf(int64_t n, const typename Real4<R>::type *__restrict__ xV, MeshP<D, R> mesh, PrefilterP pre, float4 *__restrict__ xf)
 {
-    // run r = (dx, dy) column offset in 3-D, dx in 2-D; empty when the column is outside the mesh
-    int cc[D];
-    bool inside = true;
-    if (D == 3)
-    {
-        cc[0] = c[0] + r / 3 - 1;
-        cc[1] = c[1] + r % 3 - 1;
-        inside = cc[0] >= 0 && cc[0] < mesh.cells[0] && cc[1] >= 0 && cc[1] < mesh.cells[1];
-    }
-    else
-    {
-        cc[0] = c[0] + r - 1;
-        inside = cc[0] >= 0 && cc[0] < mesh.cells[0];
-    }
-    if (!inside)
-    {
-        b = e = 0;
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
         return;
+    typename Real4<R>::type v = ldg4(xV + i);
+    R x[3] = {v.x, v.y, D == 3 ? v.z : R(0)};
+    float f[3] = {0.f, 0.f, 0.f};
+    bool inside = true;
+#pragma unroll
+    for (int d = 0; d < D; ++d)
+    {
+        const R rel = x[d] - mesh.lo[d];
+        f[d] = float(rel);
+        inside = inside && rel >= -mesh.spacing && f[d] <= pre.limit[d];
     }
-    int lo = max(c[D - 1] - 1, 0), hi = min(c[D - 1] + 1, mesh.cells[D - 1] - 1);
-    cc[D - 1] = lo;
-    u32 first = mesh.linear(cc);
-    b = __ldg(cell_offset + first);
-    e = __ldg(cell_offset + first + u32(hi - lo) + 1);
+    const float bad = __int_as_float(0x7fc00000);
+    xf[i] = inside ? make_float4(f[0], f[1], f[2], 0.f) : make_float4(bad, bad, bad, 0.f);
 }
 
-template <int D, class R, bool INNER>
+template <int D, class R, bool INNER, bool PRE>
 __global__ void __launch_bounds__(128) k_search_mask(int64_t n_src, const typename Real4<R>::type *__restrict__ xV_s,
                                                      const typename Real4<R>::type *__restrict__ xV_t,
                                                      const u32 *__restrict__ cell_offset, MeshP<D, R> mesh, R rc2,
                                                      u32 *__restrict__ count, u32 *__restrict__ slice_w,
-                                                     u32 *__restrict__ mask, int *__restrict__ overflow)
+                                                     u32 *__restrict__ mask, int *__restrict__ overflow,
+                                                     const float4 *__restrict__ xf_t, PrefilterP pre)
 {
     constexpr int W = MaskLayout<D>::words;
     int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
@@ -287,6 +286,18 @@ __global__ void __launch_bounds__(128) k_search_mask(int64_t n_src, const typena
             xi[D - 1] = v.z;
         int c[D];
         mesh.cellIndex(xi, c);
+        float xif[D];
+        if (PRE)
+        {
+#pragma unroll
+            for (int d = 0; d < D; ++d)
+            {
+                const R rel = xi[d] - mesh.lo[d];
+                xif[d] = float(rel);
+                if (!(rel >= -mesh.spacing && xif[d] <= pre.limit[d]))
+                    xif[d] = __int_as_float(0x7fc00000); // outside the mesh: every candidate takes the exact test
+            }
+        }
         u32 *mrow = mask + (u64(i >> 5) * W) * 32u + lane;
         for (int r = 0; r < MaskLayout<D>::runs; ++r)
         {
@@ -305,17 +316,57 @@ __global__ void __launch_bounds__(128) k_search_mask(int64_t n_src, const typena
                 if (j0 < e)
                 {
                     const u32 m = min(e - j0, 32u);
-#pragma unroll 4
-                    for (u32 t = 0; t < m; ++t)
+                    u32 todo = 0; // candidates that need the exact test
+                    if (PRE)
                     {
-                        typename Real4<R>::type q = ldg4(xV_t + (j0 + t));
-                        R d[D];
-                        d[0] = xi[0] - q.x;
-                        d[1] = xi[1] - q.y;
-                        if (D == 3)
-                            d[D - 1] = xi[D - 1] - q.z;
-                        R mm = sqnormExact<D, R>(d);
-                        word |= (mm < rc2 ? 1u : 0u) << t;
+#pragma unroll 8
+                        for (u32 t = 0; t < m; ++t)
+                        {
+                            const float4 q = __ldg(xf_t + (j0 + t));
+                            const float dx = xif[0] - q.x, dy = xif[1] - q.y;
+                            float mm = dx * dx + dy * dy;
+                            if (D == 3)
+                            {
+                                const float dz = xif[D - 1] - q.z;
+                                mm += dz * dz;
+                            }
+                            const bool hit = mm < pre.lo;
+                            word |= (hit ? 1u : 0u) << t;
+                            todo |= (hit || mm > pre.hi ? 0u : 1u) << t;
+                        }
+                    }
+                    else
+                        todo = m == 32u ? 0xffffffffu : (1u << m) - 1u;
+                    if (PRE)
+                    {
+                        while (todo)
+                        {
+                            const u32 t = u32(__ffs(int(todo)) - 1);
+                            todo &= todo - 1u;
+                            typename Real4<R>::type q = ldg4(xV_t + (j0 + t));
+                            R d[D];
+                            d[0] = xi[0] - q.x;
+                            d[1] = xi[1] - q.y;
+                            if (D == 3)
+                                d[D - 1] = xi[D - 1] - q.z;
+                            R mm = sqnormExact<D, R>(d);
+                            word |= (mm < rc2 ? 1u : 0u) << t;
+                        }
+                    }
+                    else
+                    {
+#pragma unroll 4
+                        for (u32 t = 0; t < m; ++t)
+                        {
+                            typename Real4<R>::type q = ldg4(xV_t + (j0 + t));
+                            R d[D];
+                            d[0] = xi[0] - q.x;
+                            d[1] = xi[1] - q.y;
+                            if (D == 3)
+                                d[D - 1] = xi[D - 1] - q.z;
+                            R mm = sqnormExact<D, R>(d);
+                            word |= (mm < rc2 ? 1u : 0u) << t;
+                        }
                     }
                     if (INNER)
                     { // NeighborBuilderInner: i != j (neighborhood.cpp:85-98)
@@ -435,6 +486,77 @@ __global__ void k_sum_u32(const u32 *__restrict__ v, int64_t n, unsigned long lo
         atomicAdd(out, s);
 }
 
+// thresholds of the fp32 pre-filter (see PrefilterP); false when the band would be too wide to be worth it
+template <int D, class R>
+static bool searchPrefilter(const MeshP<D, R> &mesh, R rc_, PrefilterP &pre)
+{
+    const char *env = getenv("SPHB200_SEARCH_PREFILTER");
+    if (env && env[0] == '0')
+        return false;
+    const double u = 1.0 / 16777216.0, rc = double(rc_), sp = double(mesh.spacing);
+    double M = 0;
+    for (int d = 0; d < 3; ++d)
+        pre.limit[d] = 0.f;
+    for (int d = 0; d < D; ++d)
+    {
+        const double ext = double(mesh.cells[d]) * sp + sp;
+        M = ext > M ? ext : M;
+        pre.limit[d] = float(ext);
+    }
+    M *= 1.0 + 4 * u; // limit[] is compared in fp32
+    const double delta = 2 * u * M + u * 4 * rc;
+    const double tau = 4.0 * (2.0 * sqrt(double(D)) * rc * delta + D * delta * delta + 4 * u * rc * rc) + 4 * u * rc * rc;
+    const double rc2 = rc * rc;
+    if (tau > 0.05 * rc2)
+        return false;
+    pre.lo = nextafterf(float(rc2 - tau), 0.f);
+    pre.hi = nextafterf(float(rc2 + tau), INFINITY);
+    return true;
+}
+
+static sphb200_status reserveList(sphb200_ctx *ctx, NeighborList &L)
+{
+    if (L.total_entries > L.cap_entries || !L.list)
+    {
+        cudaFree(L.list);
+        L.list = nullptr;
+        L.cap_entries = 0;
+        size_t cap = size_t(L.total_entries) + size_t(L.total_entries) / 8 + 1024;
+        SPHB_CUDA(ctx, cudaMalloc(&L.list, cap * 4));
+        L.cap_entries = cap;
+    }
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status expandList(sphb200_relation *r, size_t k)
+{
+    sphb200_ctx *ctx = r->ctx;
+    NeighborList &L = r->lists[k];
+    if (L.expanded)
+        return SPHB200_OK;
+    if (!L.has_mask)
+        return ctx->fail(SPHB200_ERR_INVALID, "neighbour list requested before relation_update");
+    const int64_t n = r->body->n;
+    SPHB_TRY(reserveList(ctx, L));
+    if (n > 0)
+    {
+        static bool attr_set = false; // per (D, R) instantiation
+        if (!attr_set)
+        {
+            SPHB_CUDA(ctx, cudaFuncSetAttribute(k_expand_mask<D, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kExpandSmem)));
+            attr_set = true;
+        }
+        sphb200_body *tgt = r->targets[k];
+        k_expand_mask<D, R><<<gridFor(n, kExpandBlock), kExpandBlock, kExpandSmem, ctx->stream>>>(
+            n, static_cast<const typename Real4<R>::type *>(r->body->xV.p), static_cast<const u32 *>(tgt->cell_offset.p),
+            tgt->P<D, R>().mesh, L.mask, L.slice_off, L.list);
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    L.expanded = true;
+    return SPHB200_OK;
+}
+
 template <int D, class R>
 static sphb200_status relationUpdate(sphb200_relation *r)
 {
@@ -483,6 +605,8 @@ static sphb200_status relationUpdate(sphb200_relation *r)
         {
             r->target_stamp[k] = tgt->config_stamp;
             L.build_id++;
+            L.has_mask = false;
+            L.expanded = true;
             continue;
         }
         auto *xs = static_cast<const typename Real4<R>::type *>(src->xV.p);
@@ -498,12 +622,39 @@ static sphb200_status relationUpdate(sphb200_relation *r)
             if (fast)
             {
                 const size_t words = size_t((n + 31) / 32) * 32u * size_t(MaskLayout<D>::words);
-                SPHB_CUDA(ctx, ctx->mask_buf.ensure(words * 4));
-                mask = static_cast<u32 *>(ctx->mask_buf.p);
-                if (r->inner)
-                    k_search_mask<D, R, true><<<gridFor(n, 128), 128, 0, st>>>(n, xs, xt, off, Pt.mesh, sp.rc2, L.count, L.slice_w, mask, overflow);
+                if (L.cap_mask < words)
+                {
+                    cudaFree(L.mask);
+                    L.mask = nullptr;
+                    L.cap_mask = 0;
+                    const size_t cap = words + words / 8;
+                    SPHB_CUDA(ctx, cudaMalloc(&L.mask, cap * 4));
+                    L.cap_mask = cap;
+                }
+                mask = L.mask;
+                PrefilterP pre;
+                const bool prefilter = sizeof(R) == 8 && searchPrefilter<D, R>(Pt.mesh, sp.rc, pre);
+                const float4 *xf = nullptr;
+                if (prefilter)
+                {
+                    if (tgt->xf_stamp != tgt->config_stamp || !tgt->xf.p)
+                    {
+                        SPHB_CUDA(ctx, tgt->xf.ensure(size_t(tgt->n) * sizeof(float4)));
+                        k_make_xf<D, R><<<gridFor(tgt->n, 256), 256, 0, st>>>(tgt->n, xt, Pt.mesh, pre, static_cast<float4 *>(tgt->xf.p));
+                        SPHB_LAUNCH_CHECK(ctx);
+                        tgt->xf_stamp = tgt->config_stamp;
+                    }
+                    xf = static_cast<const float4 *>(tgt->xf.p);
+                }
+                const int grid = gridFor(n, 128);
+                if (r->inner && prefilter)
+                    k_search_mask<D, R, true, true><<<grid, 128, 0, st>>>(n, xs, xt, off, Pt.mesh, sp.rc2, L.count, L.slice_w, mask, overflow, xf, pre);
+                else if (r->inner)
+                    k_search_mask<D, R, true, false><<<grid, 128, 0, st>>>(n, xs, xt, off, Pt.mesh, sp.rc2, L.count, L.slice_w, mask, overflow, xf, pre);
+                else if (prefilter)
+                    k_search_mask<D, R, false, true><<<grid, 128, 0, st>>>(n, xs, xt, off, Pt.mesh, sp.rc2, L.count, L.slice_w, mask, overflow, xf, pre);
                 else
-                    k_search_mask<D, R, false><<<gridFor(n, 128), 128, 0, st>>>(n, xs, xt, off, Pt.mesh, sp.rc2, L.count, L.slice_w, mask, overflow);
+                    k_search_mask<D, R, false, false><<<grid, 128, 0, st>>>(n, xs, xt, off, Pt.mesh, sp.rc2, L.count, L.slice_w, mask, overflow, xf, pre);
             }
             else
                 k_search<D, R, false><<<gridFor(n, 128), 128, 0, st>>>(n, xs, xt, off, sp, L.count, L.slice_w, nullptr, nullptr);
@@ -525,27 +676,17 @@ static sphb200_status relationUpdate(sphb200_relation *r)
             L.total_pairs = host_acc[0];
             break;
         }
-        if (L.total_entries > L.cap_entries || !L.list)
+        // the masked search leaves the hits as bits; the index list is written when a kernel asks for it
+        // (ensureList) - the group-tiled kernels build their union lists from the bits directly (tile.cuh)
+        L.has_mask = fast;
+        L.expanded = false;
+        if (!fast)
         {
-            cudaFree(L.list);
-            L.list = nullptr;
-            size_t cap = size_t(L.total_entries) + size_t(L.total_entries) / 8 + 1024;
-            SPHB_CUDA(ctx, cudaMalloc(&L.list, cap * 4));
-            L.cap_entries = cap;
-        }
-        if (fast)
-        {
-            static bool attr_set = false; // per (D, R) instantiation
-            if (!attr_set)
-            {
-                SPHB_CUDA(ctx, cudaFuncSetAttribute(k_expand_mask<D, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kExpandSmem)));
-                attr_set = true;
-            }
-            k_expand_mask<D, R><<<gridFor(n, kExpandBlock), kExpandBlock, kExpandSmem, st>>>(n, xs, off, Pt.mesh, mask, L.slice_off, L.list);
-        }
-        else
+            SPHB_TRY(reserveList(ctx, L));
             k_search<D, R, true><<<gridFor(n, 128), 128, 0, st>>>(n, xs, xt, off, sp, L.count, L.slice_w, L.slice_off, L.list);
-        SPHB_LAUNCH_CHECK(ctx);
+            SPHB_LAUNCH_CHECK(ctx);
+            L.expanded = true;
+        }
         r->target_stamp[k] = tgt->config_stamp;
         L.build_id++;
         L.sorted = Pt.per.mask == 0; // both non-periodic searches emit ascending j per particle
@@ -553,6 +694,12 @@ static sphb200_status relationUpdate(sphb200_relation *r)
     r->source_stamp = src->config_stamp;
     r->valid = true;
     return SPHB200_OK;
+}
+sphb200_status ensureList(sphb200_relation *r, size_t k)
+{
+    if (r->lists[k].expanded)
+        return SPHB200_OK;
+    return SPHB_DISPATCH(r->ctx, expandList, r, k);
 }
 } // namespace sphb
 
@@ -617,6 +764,8 @@ sphb200_status sphb200_relation_neighbors(sphb200_relation *r, int k, int32_t *c
         *total = int64_t(L.total_pairs);
     if (!counts && !j_out)
         return SPHB200_OK;
+    if (j_out)
+        SPHB_TRY(sphb::ensureList(r, size_t(k)));
     std::vector<u32> c, so, lst;
     c.resize(size_t(n));
     so.resize(size_t((n + kP - 1) / kP + 1));

@@ -503,6 +503,7 @@ static sphb200_status correctionMatrix(sphb200_relation *inner)
     SPHB_TRY((ensurePacked<D, R>(b)));
     R *B;
     SPHB_TRY(getVarPtr<R>(b, "LinearGradientCorrectionMatrix", D * D, &B));
+    SPHB_TRY(ensureList(inner, 0));
     k_correction_matrix<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
         b->own_begin, b->own_end, static_cast<const typename Real4<R>::type *>(b->xV.p), slistOf(inner->lists[0]), b->P<D, R>().kern, B);
     SPHB_LAUNCH_CHECK(ctx);
@@ -538,6 +539,7 @@ static sphb200_status solidFirstHalf(sphb200_relation *inner, int decomposed, do
     k_solid_first_init<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, decomposed, sp, dt, pos, vel, F, dF, B, rho,
                                                                           Jterm, stress, invFT, pk1);
     SPHB_LAUNCH_CHECK(ctx);
+    SPHB_TRY(ensureList(inner, 0));
     k_solid_first_interaction<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
         b->own_begin, b->own_end, decomposed, sp, xV, slistOf(inner->lists[0]), b->P<D, R>().kern, pos, vel, mass, stress, Jterm, F, pk1, force);
     SPHB_LAUNCH_CHECK(ctx);
@@ -562,6 +564,7 @@ static sphb200_status solidSecondHalf(sphb200_relation *inner, double dt_)
     SPHB_TRY(getVarPtr<R>(b, "LinearGradientCorrectionMatrix", D * D, &B));
     SPHB_TRY(getVarPtr<R>(b, "DeformationGradient", D * D, &F, true));
     SPHB_TRY(getVarPtr<R>(b, "DeformationRate", D * D, &dF, true));
+    SPHB_TRY(ensureList(inner, 0));
     k_solid_second_half<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
         b->own_begin, b->own_end, R(dt_), static_cast<const typename Real4<R>::type *>(b->xV.p), slistOf(inner->lists[0]), b->P<D, R>().kern,
         vel, B, pos, F, dF);
