@@ -122,6 +122,60 @@ def test_neighbor_sets_inner_and_contact(pk, gpu, oracle, ndim, dp, real_bytes, 
         assert counts.max() == (20 if ndim == 2 else 80)  # interior lattice KAT, SURVEY §8c
 
 
+def test_search_prefilter_is_exact(pk, gpu):
+    """relation.cu: the fp32 pre-filter of the fp64 search may only decide what the exact test
+    (neighborhood.cpp:85-98: d.d < rc^2 on the fp64 positions) decides the same way.  Random particles far from
+    the mesh origin (coarse fp32 grid), partners placed within 1e-9 rc of the cut-off, and particles outside
+    the mesh; the lists with and without the pre-filter must be identical, and the borderline pairs must follow
+    the fp64 arithmetic."""
+    import os
+    rng = np.random.default_rng(7)
+    dp = 0.05
+    rc = 2 * 1.3 * dp
+    n0 = 150_000
+    x = 36.0 + 2.0 * rng.random((n0, 3))
+    m = 20_000
+    u = rng.normal(size=(m, 3))
+    u /= np.linalg.norm(u, axis=1)[:, None]
+    eps = rng.uniform(-1e-9, 1e-9, m)
+    eps[:64] = np.linspace(-2e-15, 2e-15, 64)
+    partners = x[:m] + u * (rc * (1.0 + eps))[:, None]
+    out = np.array([[-3.0, 37.0, 37.0], [37.0, 45.0, 37.0], [44.9, 37.0, 37.0], [44.9, 37.0, 37.05]])
+    pos = np.concatenate([x, partners, out])
+    res = []
+    for flag in ("1", "0"):
+        os.environ["SPHB200_SEARCH_PREFILTER"] = flag
+        try:
+            s = gpu.SPHSystem(3, [0, 0, 0], [40, 40, 40], dp)
+            b = s.add_body("b", len(pos), dp)
+            b.set("Position", pos)
+            b.set("VolumetricMeasure", np.full(len(pos), dp ** 3))
+            b.update_cell_list()
+            rel = s.inner(b)
+            rel.update()
+            counts, j = rel.neighbors()
+            oid, _ = b.ids()
+            xs = b.get("Position")
+            res.append((counts.copy(), j.copy(), oid.copy(), xs.copy()))
+            s.close()
+        finally:
+            os.environ.pop("SPHB200_SEARCH_PREFILTER", None)
+    (c1, j1, o1, x1), (c0, j0, o0, _) = res
+    assert np.array_equal(o1, o0) and np.array_equal(c1, c0) and np.array_equal(j1, j0)
+    # the borderline pairs against the fp64 arithmetic of the exact test
+    start = np.concatenate([[0], np.cumsum(c1)])
+    where = np.empty(len(pos), dtype=np.int64)
+    where[o1] = np.arange(len(pos))
+    listed = 0
+    for k in range(0, m, 97):
+        i, p = where[k], where[n0 + k]
+        d = x1[i] - x1[p]
+        inside = (d[0] * d[0] + d[1] * d[1] + d[2] * d[2]) < rc * rc
+        assert (p in j1[start[i]:start[i + 1]]) == bool(inside)
+        listed += bool(inside)
+    assert 0 < listed < len(range(0, m, 97))
+
+
 def test_neighbor_sets_periodic(pk, gpu, oracle):
     g, o = both(pk, gpu, oracle, pk.cases.TaylorGreen, dp=0.02)
     pg, po = pair_set(g.inner), pair_set(o.inner)
