@@ -944,20 +944,25 @@ static sphb200_status densitySummation(sphb200_relation *inner, sphb200_relation
     SPHB_TRY((ensurePacked<D, R>(b)));
     ContactP<R> ct;
     KernelP<R> kern_ct = P.kern;
-    SPHB_TRY((makeContactP<D, R>(contact, 1, ct, kern_ct)));
+    const bool tiled = tileUsable<D, R>(inner, contact);
+    SPHB_TRY((makeContactP<D, R>(contact, tiled ? 1 | 16 : 1, ct, kern_ct)));
     R *mass, *rho_sum, *rho, *vol;
     SPHB_TRY(getVarPtr<R>(b, "Mass", 1, &mass, true));
     SPHB_TRY(getVarPtr<R>(b, "DensitySummation", 1, &rho_sum));
     SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
     SPHB_TRY(getVarPtr<R>(b, "VolumetricMeasure", 1, &vol, true));
     auto *xV = static_cast<typename Real4<R>::type *>(b->xV.p);
-    if (tileUsable<D, R>(inner, contact))
+    if (tiled)
     {
         constexpr int G = TileG<R>::value;
         SPHB_TRY((ensureUnion<D, R, G>(inner, 0, inner->lists[0].uni, 1)));
         const UnionList &U = inner->lists[0].uni;
+        UContactP<R> uct;
+        uct.n = 0;
+        if (contact)
+            SPHB_TRY((makeUContactP<D, R>(contact, ct, uct, false)));
         k_density_summation_tile<D, R, G><<<gridFor(U.n_groups, 128), 128, 0, ctx->stream>>>(
-            U.base, b->own_begin, b->own_end, U.n_groups, xV, ulistOf(U), ct, P.kern, kern_ct, R(b->rho0), R(1.0) / P.sigma0, mass, rho_sum,
+            U.base, b->own_begin, b->own_end, U.n_groups, xV, ulistOf(U), ct, uct, P.kern, kern_ct, R(b->rho0), R(1.0) / P.sigma0, mass, rho_sum,
             rho, vol, xV, free_surface);
     }
     else
