@@ -83,6 +83,14 @@ sphb200_status sphb200_var_to_host(sphb200_body *b, const char *name);
 /* explicit-buffer variants (host buffer of n*width Reals) */
 sphb200_status sphb200_var_upload(sphb200_body *b, const char *name, const void *src);
 sphb200_status sphb200_var_download(sphb200_body *b, const char *name, void *dst);
+/* Double-buffered upload.  var_stage starts an asynchronous copy of a host buffer (n*width Reals; pinned memory
+ * for a real overlap, and untouched until the commit) into a staging mirror on the context's copy stream - the
+ * dynamics queued on the compute stream keep running on the current mirrors.  body_commit_staged makes the compute
+ * stream wait for those copies and swaps every staged mirror in (like var_upload, the variables count as rewritten:
+ * call cell_list_update afterwards).  The SYCL twin is the queue-ordered copy of
+ * src_sycl/shared/common/sphinxsys_variable_sycl.hpp:35-87, which the host thread does not wait for either. */
+sphb200_status sphb200_var_stage(sphb200_body *b, const char *name, const void *src);
+sphb200_status sphb200_body_commit_staged(sphb200_body *b);
 /* DelegatedData(par_device): raw device pointer, valid until the next cell_list_update of b */
 sphb200_status sphb200_var_device_ptr(sphb200_body *b, const char *name, void **out);
 /* Reals per particle of a registered variable (DiscreteVariable<T>: sizeof(T)/sizeof(Real),

@@ -44,6 +44,8 @@ SIGNATURES = {
     "sphb200_var_to_host": (_i, [_vp, _cp]),
     "sphb200_var_upload": (_i, [_vp, _cp, _vp]),
     "sphb200_var_download": (_i, [_vp, _cp, _vp]),
+    "sphb200_var_stage": (_i, [_vp, _cp, _vp]),
+    "sphb200_body_commit_staged": (_i, [_vp]),
     "sphb200_var_device_ptr": (_i, [_vp, _cp, _vpp]),
     "sphb200_var_width": (_i, [_vp, _cp, C.POINTER(C.c_int)]),
     "sphb200_ids_to_host": (_i, [_vp, _i64p, _i64p]),

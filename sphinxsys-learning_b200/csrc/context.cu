@@ -227,6 +227,8 @@ void sphb200_ctx_destroy(sphb200_ctx *ctx)
         return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream)
+        cudaStreamSynchronize(ctx->copy_stream);
     for (auto *r : ctx->relations)
     {
         for (auto &l : r->lists)
@@ -255,6 +257,7 @@ void sphb200_ctx_destroy(sphb200_ctx *ctx)
         {
             kv.second->dev.release();
             kv.second->alt.release();
+            kv.second->stage.release();
         }
         for (DevBuf *d : {&b->original_id, &b->sorted_id, &b->cell_of, &b->rank_in_cell, &b->perm, &b->cell_count,
                           &b->cell_offset, &b->xV, &b->tmp_var, &b->rec_a, &b->rec_b, &b->vol_mm, &b->xf})
@@ -265,6 +268,13 @@ void sphb200_ctx_destroy(sphb200_ctx *ctx)
         d->release();
     if (ctx->reduce_host)
         cudaFreeHost(ctx->reduce_host);
+    if (ctx->copy_stream)
+    {
+        cudaStreamSynchronize(ctx->copy_stream);
+        cudaStreamDestroy(ctx->copy_stream);
+        cudaEventDestroy(ctx->copy_done);
+        cudaEventDestroy(ctx->mirrors_free);
+    }
     if (ctx->owns_stream)
         cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -419,6 +429,64 @@ sphb200_status sphb200_var_upload(sphb200_body *b, const char *name, const void 
     SPHB_CUDA(ctx, cudaMemcpyAsync(v->dev.p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
     SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); // src may be pageable and reused by the caller
     touched(b, name);
+    return SPHB200_OK;
+}
+sphb200_status sphb200_var_stage(sphb200_body *b, const char *name, const void *src)
+{
+    if (!b || !name || !src)
+        return SPHB200_ERR_INVALID;
+    sphb200_ctx *ctx = b->ctx;
+    Var *v = b->find(name);
+    if (!v)
+        return ctx->fail(SPHB200_ERR_NOT_FOUND, std::string("variable '") + name + "' is not registered");
+    cudaSetDevice(ctx->device);
+    if (!ctx->copy_stream)
+    {
+        SPHB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        SPHB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->copy_done, cudaEventDisableTiming));
+        SPHB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->mirrors_free, cudaEventDisableTiming));
+    }
+    const size_t bytes = size_t(b->n) * size_t(v->width) * size_t(ctx->real_bytes);
+    if (v->stage.bytes < bytes)
+    { // first use (or the body grew): the allocation synchronises the device once
+        v->stage.release();
+        SPHB_CUDA(ctx, v->stage.ensure(bytes));
+    }
+    // the staging mirror was a live mirror until the last commit: kernels queued before it may still read it
+    SPHB_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->mirrors_free, 0));
+    SPHB_CUDA(ctx, cudaMemcpyAsync(v->stage.p, src, bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+    v->staged_n = b->n;
+    return SPHB200_OK;
+}
+sphb200_status sphb200_body_commit_staged(sphb200_body *b)
+{
+    if (!b)
+        return SPHB200_ERR_INVALID;
+    sphb200_ctx *ctx = b->ctx;
+    cudaSetDevice(ctx->device);
+    bool any = false;
+    for (auto &kv : b->vars)
+        if (kv.second->staged_n >= 0)
+        {
+            if (kv.second->staged_n != b->n)
+                return ctx->fail(SPHB200_ERR_INVALID, "commit_staged: body '" + b->name + "' was resized after var_stage of '" + kv.first + "'");
+            any = true;
+        }
+    if (!any)
+        return SPHB200_OK;
+    SPHB_CUDA(ctx, cudaEventRecord(ctx->copy_done, ctx->copy_stream));
+    SPHB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->copy_done, 0));
+    for (auto &kv : b->vars)
+    {
+        Var &v = *kv.second;
+        if (v.staged_n < 0)
+            continue;
+        std::swap(v.dev, v.stage);
+        v.staged_n = -1;
+        touched(b, kv.first.c_str());
+    }
+    // what is now the staging side may be overwritten once everything queued so far has run
+    SPHB_CUDA(ctx, cudaEventRecord(ctx->mirrors_free, ctx->stream));
     return SPHB200_OK;
 }
 sphb200_status sphb200_var_download(sphb200_body *b, const char *name, void *dst)

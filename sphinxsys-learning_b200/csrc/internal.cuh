@@ -206,6 +206,8 @@ struct Var
     void *host = nullptr;
     DevBuf dev;
     DevBuf alt; // destination of the next cell-order gather (swapped with dev; no allocation per sort)
+    DevBuf stage;          // target of var_stage, swapped with dev by body_commit_staged
+    int64_t staged_n = -1; // particles the staged copy holds, -1: nothing staged
 };
 } // namespace sphb
 
@@ -215,6 +217,8 @@ struct sphb200_ctx
     double sys_lo[3] = {0, 0, 0}, sys_hi[3] = {0, 0, 0};
     cudaStream_t stream = nullptr;
     bool owns_stream = true;
+    cudaStream_t copy_stream = nullptr; // var_stage copies (created on first use)
+    cudaEvent_t copy_done = nullptr, mirrors_free = nullptr;
     std::string error;
     int64_t launches = 0;
     int pair_kernel = -2; // -2: process default (env SPHB200_TILE), -1 auto, 0 per-particle lists, 1 group-tiled

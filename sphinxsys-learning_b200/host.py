@@ -216,6 +216,13 @@ class Body:
         if self.n:
             self.sys.check(self.lib.sphb200_var_upload(self.h, name.encode(), a.ctypes.data_as(C.c_void_p)))
 
+    def stage(self, name, host_ptr):
+        """asynchronous upload of a (pinned) host buffer into the staging mirror; commit_staged() swaps it in"""
+        self.sys.check(self.lib.sphb200_var_stage(self.h, name.encode(), C.c_void_p(host_ptr)))
+
+    def commit_staged(self):
+        self.sys.check(self.lib.sphb200_body_commit_staged(self.h))
+
     def width(self, name):
         w = C.c_int()
         self.sys.check(self.lib.sphb200_var_width(self.h, name.encode(), C.byref(w)))

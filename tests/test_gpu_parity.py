@@ -329,6 +329,41 @@ def test_twisting_column_steps_match_oracle(pk, gpu, oracle, decomposed):
 # ------------------------------------------------------------------------------------------------
 # error behaviour and edge cases
 # ------------------------------------------------------------------------------------------------
+def test_staged_upload_equals_upload(pk, gpu):
+    """sphb200_var_stage + sphb200_body_commit_staged (double-buffered, copy stream) must leave the body exactly
+    as sphb200_var_upload does, including when the staging mirrors are reused step after step"""
+    names = ("Position", "Velocity", "Density", "Pressure", "DensityChangeRate", "Force", "ForcePrior", "Mass",
+             "VolumetricMeasure")
+    a = pk.cases.DamBreak(gpu, ndim=3, dp=0.05, real_bytes=8)
+    b = pk.cases.DamBreak(gpu, ndim=3, dp=0.05, real_bytes=8)
+    for _ in range(2):
+        a.advection_step()
+        b.advection_step()
+    # both bodies are given the same arrays slot by slot, so they must stay identical slot by slot
+    host = {nm: np.ascontiguousarray(a.water.get(nm)) for nm in names}
+    for rounds in range(3):
+        for c, staged in ((a, False), (b, True)):
+            w = c.water
+            if staged:
+                for nm in names:
+                    w.stage(nm, host[nm].ctypes.data)
+                w.commit_staged()
+            else:
+                for nm in names:
+                    w.set(nm, host[nm])
+            w.update_cell_list()
+            c.update_configuration()
+            c.advection_step()
+        for nm in ("Position", "Velocity", "Density", "Force"):
+            assert np.array_equal(a.water.get(nm), b.water.get(nm)), (rounds, nm)
+        assert a.dt == b.dt
+    # a resize between stage and commit is refused
+    b.water.stage("Density", host["Density"].ctypes.data)
+    b.water.resize(b.water.n - 1)
+    with pytest.raises(Exception):
+        b.water.commit_staged()
+
+
 def test_errors_and_empty_bodies(pk, gpu):
     s = gpu.SPHSystem(3, [0, 0, 0], [1, 1, 1], 0.1)
     empty = s.add_body("empty", 0, 0.1)
