@@ -260,7 +260,7 @@ void sphb200_ctx_destroy(sphb200_ctx *ctx)
             kv.second->stage.release();
         }
         for (DevBuf *d : {&b->original_id, &b->sorted_id, &b->cell_of, &b->rank_in_cell, &b->perm, &b->cell_count,
-                          &b->cell_offset, &b->xV, &b->tmp_var, &b->rec_a, &b->rec_b, &b->vol_mm, &b->xf})
+                          &b->cell_offset, &b->xV, &b->tmp_var, &b->rec_a, &b->rec_b, &b->vol_mm, &b->xf, &b->wall_sum})
             d->release();
         delete b;
     }

@@ -835,6 +835,13 @@ static bool tileUsable(sphb200_relation *inner, sphb200_relation *wall)
                 return false;
     return true;
 }
+// wall pre-pass of the tiled pair kernels (tile.cuh): one contact body, one thread per union list
+static bool wallPrepass(sphb200_relation *wall)
+{
+    const char *e = getenv("SPHB200_WALL_PREPASS"); // read per call: the parity test runs both ways in one process
+    const bool on = !(e && e[0] == '0');
+    return on && wall && wall->lists.size() == 1 && kWideLanes == 1;
+}
 template <int D, class R>
 static sphb200_status makeUContactP(sphb200_relation *wall, const ContactP<R> &cp, UContactP<R> &out, bool wide)
 {
@@ -1052,10 +1059,24 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
             UContactP<R> uw;
             SPHB_TRY((makeUContactP<D, R>(wall, wp, uw, false)));
             const UnionList &U = inner->lists[0].uni;
-            k_first_half_tile<D, R, G><<<gridFor(U.n_groups, 128), 128, 0, ctx->stream>>>(
-                U.base, b->own_begin, b->own_end, U.n_groups, rec_a, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern),
-                makeTileKernelP<R>(kern_w), fl, dt, rho, mass, fprior, force, drho, vel, slot,
-                static_cast<const unsigned long long *>(b->vol_mm.p));
+            auto *vmm = static_cast<const unsigned long long *>(b->vol_mm.p);
+            if (wallPrepass(wall))
+            {
+                UnionList &UW = wall->lists[0].uni;
+                SPHB_TRY(ensureActive(ctx, UW));
+                SPHB_CUDA(ctx, b->wall_sum.ensure(size_t(b->n) * (D + 1) * sizeof(R)));
+                R *ws = static_cast<R *>(b->wall_sum.p);
+                k_first_half_wall<D, R, G><<<148 * 4, 128, 0, ctx->stream>>>(UW.base, b->own_begin, b->own_end, UW.queue, rec_a, uw.t[0],
+                                                                           makeTileKernelP<R>(kern_w), rho, mass, fprior, ws);
+                SPHB_LAUNCH_CHECK(ctx);
+                k_first_half_tile<D, R, G, true><<<gridFor(U.n_groups, 128), 128, 0, ctx->stream>>>(
+                    U.base, b->own_begin, b->own_end, U.n_groups, rec_a, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern),
+                    makeTileKernelP<R>(kern_w), fl, dt, rho, mass, fprior, force, drho, vel, slot, vmm, ws);
+            }
+            else
+                k_first_half_tile<D, R, G, false><<<gridFor(U.n_groups, 128), 128, 0, ctx->stream>>>(
+                    U.base, b->own_begin, b->own_end, U.n_groups, rec_a, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern),
+                    makeTileKernelP<R>(kern_w), fl, dt, rho, mass, fprior, force, drho, vel, slot, vmm, nullptr);
         }
         else if (P.per.mask)
             k_first_half<D, R, true><<<grid, 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_a, rec_b, listOf<R>(inner->lists[0]), wp,
@@ -1120,9 +1141,23 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
         UContactP<R> uw;
         SPHB_TRY((makeUContactP<D, R>(wall, wp, uw, true)));
         const int64_t n_threads = (b->own_end - U.base + G - 1) / G;
-        k_second_half_tile<D, R, G, kWideLanes><<<gridFor(n_threads, 128), 128, 0, ctx->stream>>>(
-            U.base, b->own_begin, b->own_end, n_threads, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern), makeTileKernelP<R>(kern_w), fl,
-            R(dt_), pos, rho, drho, force);
+        if (wallPrepass(wall))
+        {
+            UnionList &UW = wall->lists[0].uni;
+            SPHB_TRY(ensureActive(ctx, UW));
+            SPHB_CUDA(ctx, b->wall_sum.ensure(size_t(b->n) * (D + 1) * sizeof(R)));
+            R *ws = static_cast<R *>(b->wall_sum.p);
+            k_second_half_wall<D, R, G><<<148 * 4, 128, 0, ctx->stream>>>(UW.base, b->own_begin, b->own_end, UW.queue, rec_b, uw.t[0],
+                                                                        makeTileKernelP<R>(kern_w), R(fl.limiter_slope * fl.inv_c0_ave), ws);
+            SPHB_LAUNCH_CHECK(ctx);
+            k_second_half_tile<D, R, G, kWideLanes, true><<<gridFor(n_threads, 128), 128, 0, ctx->stream>>>(
+                U.base, b->own_begin, b->own_end, n_threads, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern), makeTileKernelP<R>(kern_w),
+                fl, R(dt_), pos, rho, drho, force, ws);
+        }
+        else
+            k_second_half_tile<D, R, G, kWideLanes, false><<<gridFor(n_threads, 128), 128, 0, ctx->stream>>>(
+                U.base, b->own_begin, b->own_end, n_threads, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern), makeTileKernelP<R>(kern_w),
+                fl, R(dt_), pos, rho, drho, force, nullptr);
     }
     else if (P.per.mask)
         k_second_half<D, R, true><<<groupGrid(b->own_begin, b->own_end, 128), 128, 0, ctx->stream>>>(b->own_begin, b->own_end, rec_b, listOf<R>(inner->lists[0]), wp,

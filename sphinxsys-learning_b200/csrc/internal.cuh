@@ -148,6 +148,8 @@ struct UnionList
     int64_t base = 0, n_groups = 0, own_begin = -1, own_end = -1;
     u64 total_entries = 0;
     uint64_t build_id = 0; // NeighborList::build_id this union was merged from
+    uint64_t active_build = 0; // build whose non-empty groups are listed in queue (tile.cuh ensureActive)
+    bool active_valid = false;
 };
 
 struct NeighborList
@@ -252,6 +254,7 @@ struct sphb200_body
     sphb::DevBuf xV;                                 // Real4[n]: frozen position + Vol
     sphb::DevBuf rec_a, rec_b;                       // Rec8[n]: {xV | p, v} before / after the 1st-half update
     sphb::DevBuf vol_mm;                             // u64[2]: bit patterns of min / max of xV[].w (Vol), see refreshVolRange
+    sphb::DevBuf wall_sum;                           // Real[n][D+1]: wall sums of the pair kernels' pre-pass (tile.cuh)
     sphb::DevBuf xf;                                 // float4[n]: fp32 copy of (x - mesh.lo) for the search pre-filter (relation.cu)
     uint64_t xf_stamp = ~uint64_t(0);                // config_stamp xf was made from
     bool rec_b_valid = false;                        // rec_b matches xV, Pressure and Velocity

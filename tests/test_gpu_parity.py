@@ -329,6 +329,27 @@ def test_twisting_column_steps_match_oracle(pk, gpu, oracle, decomposed):
 # ------------------------------------------------------------------------------------------------
 # error behaviour and edge cases
 # ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("ndim,dp", [(3, 0.05), (2, 0.025)])
+def test_wall_prepass_equals_in_kernel_wall_sums(pk, gpu, ndim, dp):
+    """tile.cuh: the wall sums formed by the dense pre-pass kernels are the ones the pair kernels form themselves
+    (same arithmetic, same order): whole steps must agree bit for bit"""
+    import os
+    runs = []
+    for flag in ("1", "0"):
+        os.environ["SPHB200_WALL_PREPASS"] = flag
+        try:
+            c = pk.cases.DamBreak(gpu, ndim=ndim, dp=dp, real_bytes=8)
+            c.sys.set_pair_kernel(1)
+            for _ in range(6):
+                c.advection_step()
+            runs.append({nm: c.water.get(nm) for nm in ("Position", "Velocity", "Density", "Force", "DensityChangeRate")})
+            runs[-1]["dt"] = c.dt
+        finally:
+            os.environ.pop("SPHB200_WALL_PREPASS", None)
+    for nm in runs[0]:
+        assert np.array_equal(runs[0][nm], runs[1][nm]), nm
+
+
 def test_staged_upload_equals_upload(pk, gpu):
     """sphb200_var_stage + sphb200_body_commit_staged (double-buffered, copy stream) must leave the body exactly
     as sphb200_var_upload does, including when the staging mirrors are reused step after step"""
