@@ -251,6 +251,55 @@ __global__ void __launch_bounds__(256) k_permute(const T *__restrict__ src, T *_
     dst[t] = src[int64_t(perm[i]) * width + d];
 }
 
+// the same gather for the common widths (1, 2, 3): a thread moves two consecutive particles, W loads in flight per
+// particle and W two-element (8/16-byte) stores, which are aligned because the pair starts at an even particle
+template <class T>
+struct Vec2Of;
+template <>
+struct Vec2Of<float>
+{
+    typedef float2 type;
+};
+template <>
+struct Vec2Of<double>
+{
+    typedef double2 type;
+};
+template <class T, int W>
+__global__ void __launch_bounds__(256) k_permute_w(const T *__restrict__ src, T *__restrict__ dst, const u32 *__restrict__ perm, int64_t n)
+{
+    const int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    const int64_t i = 2 * t;
+    if (i >= n)
+        return;
+    T v[2 * W];
+    const int64_t p0 = int64_t(perm[i]), p1 = i + 1 < n ? int64_t(perm[i + 1]) : p0;
+#pragma unroll
+    for (int d = 0; d < W; ++d)
+    {
+        v[d] = src[p0 * W + d];
+        v[W + d] = src[p1 * W + d];
+    }
+    if (i + 1 < n)
+    {
+        typename Vec2Of<T>::type *out = reinterpret_cast<typename Vec2Of<T>::type *>(dst + i * W);
+#pragma unroll
+        for (int d = 0; d < W; ++d)
+        {
+            typename Vec2Of<T>::type o;
+            o.x = v[2 * d];
+            o.y = v[2 * d + 1];
+            out[d] = o;
+        }
+    }
+    else
+    {
+#pragma unroll
+        for (int d = 0; d < W; ++d)
+            dst[i * W + d] = v[d];
+    }
+}
+
 __global__ void __launch_bounds__(256) k_permute_ids(const u32 *__restrict__ oid_src, u32 *__restrict__ oid_dst,
                                                      u32 *__restrict__ sorted_id, const u32 *__restrict__ cell_src,
                                                      u32 *__restrict__ cell_dst, const u32 *__restrict__ perm, int64_t n)
@@ -445,8 +494,17 @@ static sphb200_status cellListUpdate(sphb200_body *b)
         {
             Var &v = *kv.second;
             SPHB_CUDA(ctx, v.alt.ensure(size_t(n) * size_t(v.width) * sizeof(R)));
-            k_permute<R><<<gridFor(n * v.width, 256), 256, 0, st>>>(static_cast<const R *>(v.dev.p),
-                                                                    static_cast<R *>(v.alt.p), perm, n, v.width);
+            const R *vs = static_cast<const R *>(v.dev.p);
+            R *vd = static_cast<R *>(v.alt.p);
+            const int pair_grid = gridFor((n + 1) / 2, 256);
+            if (v.width == 1)
+                k_permute_w<R, 1><<<pair_grid, 256, 0, st>>>(vs, vd, perm, n);
+            else if (v.width == 2)
+                k_permute_w<R, 2><<<pair_grid, 256, 0, st>>>(vs, vd, perm, n);
+            else if (v.width == 3)
+                k_permute_w<R, 3><<<pair_grid, 256, 0, st>>>(vs, vd, perm, n);
+            else
+                k_permute<R><<<gridFor(n * v.width, 256), 256, 0, st>>>(vs, vd, perm, n, v.width);
             SPHB_LAUNCH_CHECK(ctx);
             std::swap(v.dev, v.alt);
         }
