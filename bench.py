@@ -161,7 +161,7 @@ def slab_main(a, pk, stream, rank, world, local_rank, warmup):
     k_ms = k0.elapsed_time(k1) / reps
     peak, peak_src = peaks()
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_second_half (Integration2ndHalf inner+wall) on rank 0's slab",
+    roofline = {"bound": "hbm", "kernel": "k_second_half_tile (Integration2ndHalf inner+wall) on rank 0's slab",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "peak_source": peak_src, "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg_bytes,
                 "pairs_per_particle": pairs / max(owned, 1)}
@@ -329,7 +329,7 @@ def main():
             traffic = tj[key]["dram_bytes_per_launch"]
     except Exception:
         traffic = None
-    roofline = {"bound": "hbm", "kernel": "Integration2ndHalf inner+wall, fused init/update (k_second_half_tile in fp64, k_second_half in fp32)",
+    roofline = {"bound": "hbm", "kernel": "Integration2ndHalf inner+wall, fused init/update (k_second_half_tile; wall sums from k_second_half_wall)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "peak_source": peak_src, "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg_bytes,
                 "pairs_per_particle": (pairs_in + pairs_w) / n_f}

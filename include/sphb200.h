@@ -49,7 +49,7 @@ void *sphb200_ctx_stream(sphb200_ctx *ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 int64_t sphb200_ctx_launch_count(sphb200_ctx *ctx);
 /* which pair-sum kernels the acoustic sub-step uses: -1 automatic (default: group-tiled kernels on union
- * neighbour lists for fp64, list-per-particle kernels for fp32 and for periodic bodies), 0 always
+ * neighbour lists, list-per-particle kernels for periodic bodies), 0 always
  * list-per-particle, 1 group-tiled wherever the lists allow it.  Both give the reference's sums; the knob exists
  * for A/B timing and for the parity tests of both paths (env SPHB200_TILE sets the process-wide default). */
 sphb200_status sphb200_ctx_set_pair_kernel(sphb200_ctx *ctx, int mode);

@@ -807,10 +807,11 @@ namespace sphb
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
-// The register-tiled kernels (tile.cuh) serve non-periodic fp64 bodies by default: measured on B200 at
-// 20 M particles K2/K3 take 9.68/9.47 ms tiled against 11.36/10.56 ms per-particle in fp64, but 4.41/4.20
-// against 4.37/4.07 ms in fp32 (issue-bound there, the masked pairs cost more than the saved gathers).
-// SPHB200_TILE=0 / 1 forces the choice for both precisions (A/B timing and the parity tests of both paths).
+// The register-tiled kernels (tile.cuh) serve non-periodic bodies by default.  Measured on B200 at 20 M
+// particles, ms K1+K2 / K3 / density / advection step: fp64 6.35 / 8.59 / 4.3 / 97 tiled against 11.4 / 10.6 / 6.4 / 140
+// per-particle; fp32 4.32 / 3.84 / 2.6 / 59.4 against 4.38 / 4.09 / 3.9 / 62.1 (fp32 is issue-bound, the masked pairs
+// cost nearly what the saved gathers give; the step gains because no index list has to be written).
+// SPHB200_TILE=0 / 1 forces the choice (A/B timing and the parity tests of both paths).
 static int tileMode()
 {
     static int mode = -2;
@@ -825,7 +826,7 @@ template <int D, class R>
 static bool tileUsable(sphb200_relation *inner, sphb200_relation *wall)
 {
     const int mode = inner->ctx->pair_kernel == -2 ? tileMode() : inner->ctx->pair_kernel;
-    if (mode == 0 || (mode < 0 && sizeof(R) == 4))
+    if (mode == 0)
         return false;
     if (inner->body->P<D, R>().per.mask || !inner->lists[0].sorted)
         return false;
