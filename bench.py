@@ -99,6 +99,25 @@ def slab_dp(dp1, world):
     return 1.0 / round((1.0 / dp1) * world ** (1.0 / 3.0))
 
 
+# stdout carries the one JSON line and nothing else: the process's fd 1 is pointed at stderr for the whole run
+# (NCCL prints its version banner to stdout from C at the first communicator, whatever NCCL_DEBUG level is set)
+_JSON_OUT = None
+
+
+def claim_stdout():
+    global _JSON_OUT
+    if _JSON_OUT is None:
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    claim_stdout()
+    _JSON_OUT.write(line + "\n")
+    _JSON_OUT.flush()
+
+
 def slab_main(a, pk, stream, rank, world, local_rank, warmup):
     """N > 1: one x-slab per GPU with halo exchange + migration over NCCL; no replicas."""
     import torch
@@ -218,11 +237,12 @@ def slab_main(a, pk, stream, rank, world, local_rank, warmup):
                           "page_cuts": [int(c) for c in case.cuts], "build_seconds": round(t_build, 1)},
                "roofline": roofline, "step_roofline_frac": step_frac, "a_step_bytes": a_step,
                "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
-        print(json.dumps(out))
+        emit(json.dumps(out))
     dist.destroy_process_group()
 
 
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=6)
@@ -243,7 +263,7 @@ def main():
         if rank != 0:
             return
         base, ms = cpu_reference_run(a.cpu_dp, max(a.steps, 1), 1)
-        print(json.dumps({"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": a.gpus,
+        emit(json.dumps({"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": a.gpus,
                           "steps": a.steps, "warmup": 1, "ms_per_step": ms * 1e3, "higher_is_better": True, "scaling": "weak",
                           "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                           "config": {"workload": "test_3d_dambreak lattice, bounded CPU sample", "dp": a.cpu_dp},
@@ -406,7 +426,7 @@ def main():
                           "parallelism": "1 slab per GPU" if world > 1 else "single GPU", "build_seconds": round(t_build, 1)},
                "roofline": roofline, "step_roofline_frac": step_frac, "a_step_bytes": a_step,
                "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
-        print(json.dumps(out))
+        emit(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
 
