@@ -319,10 +319,15 @@ __global__ void __launch_bounds__(128) k_search_mask(int64_t n_src, const typena
                     u32 todo = 0; // candidates that need the exact test
                     if (PRE)
                     {
+                        // the kernel is issue-bound on the integer pipe: the two decisions are taken as sign bits
+                        // (mm - lo < 0: hit, hi - mm < 0: miss; a NaN is 0x7fffffff in fp32, sign clear: undecided)
+                        // and shifted into the words by one funnel shift each; candidate t lands on bit m-1-t
+                        const float4 *cand = xf_t + j0;
+                        u32 hits = 0u, decided = 0u;
 #pragma unroll 8
                         for (u32 t = 0; t < m; ++t)
                         {
-                            const float4 q = __ldg(xf_t + (j0 + t));
+                            const float4 q = __ldg(cand + t);
                             const float dx = xif[0] - q.x, dy = xif[1] - q.y;
                             float mm = dx * dx + dy * dy;
                             if (D == 3)
@@ -330,10 +335,13 @@ __global__ void __launch_bounds__(128) k_search_mask(int64_t n_src, const typena
                                 const float dz = xif[D - 1] - q.z;
                                 mm += dz * dz;
                             }
-                            const bool hit = mm < pre.lo;
-                            word |= (hit ? 1u : 0u) << t;
-                            todo |= (hit || mm > pre.hi ? 0u : 1u) << t;
+                            const u32 a = __float_as_uint(mm - pre.lo), b = __float_as_uint(pre.hi - mm);
+                            hits = __funnelshift_l(a, hits, 1);
+                            decided = __funnelshift_l(a | b, decided, 1);
                         }
+                        const u32 live = m == 32u ? 0xffffffffu : (1u << m) - 1u;
+                        word = __brev(hits) >> (32u - m);
+                        todo = ~(__brev(decided) >> (32u - m)) & live;
                     }
                     else
                         todo = m == 32u ? 0xffffffffu : (1u << m) - 1u;
