@@ -363,17 +363,38 @@ __global__ void __launch_bounds__(128) k_search_mask(int64_t n_src, const typena
                     }
                     else
                     {
-#pragma unroll 4
-                        for (u32 t = 0; t < m; ++t)
+                        const typename Real4<R>::type *cand = xV_t + j0;
+                        if (sizeof(R) == 4)
+                        { // fp32 build: mm < rc2 as the sign of mm - rc2 (exact for finite values, clear for a NaN)
+                            u32 hits = 0u;
+#pragma unroll 8
+                            for (u32 t = 0; t < m; ++t)
+                            {
+                                typename Real4<R>::type q = ldg4(cand + t);
+                                R d[D];
+                                d[0] = xi[0] - q.x;
+                                d[1] = xi[1] - q.y;
+                                if (D == 3)
+                                    d[D - 1] = xi[D - 1] - q.z;
+                                const float diff = float(sqnormExact<D, R>(d)) - float(rc2);
+                                hits = __funnelshift_l(__float_as_uint(diff), hits, 1);
+                            }
+                            word = __brev(hits) >> (32u - m);
+                        }
+                        else
                         {
-                            typename Real4<R>::type q = ldg4(xV_t + (j0 + t));
-                            R d[D];
-                            d[0] = xi[0] - q.x;
-                            d[1] = xi[1] - q.y;
-                            if (D == 3)
-                                d[D - 1] = xi[D - 1] - q.z;
-                            R mm = sqnormExact<D, R>(d);
-                            word |= (mm < rc2 ? 1u : 0u) << t;
+#pragma unroll 4
+                            for (u32 t = 0; t < m; ++t)
+                            {
+                                typename Real4<R>::type q = ldg4(cand + t);
+                                R d[D];
+                                d[0] = xi[0] - q.x;
+                                d[1] = xi[1] - q.y;
+                                if (D == 3)
+                                    d[D - 1] = xi[D - 1] - q.z;
+                                R mm = sqnormExact<D, R>(d);
+                                word |= (mm < rc2 ? 1u : 0u) << t;
+                            }
                         }
                     }
                     if (INNER)
