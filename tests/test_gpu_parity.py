@@ -176,6 +176,38 @@ def test_search_prefilter_is_exact(pk, gpu):
     assert 0 < listed < len(range(0, m, 97))
 
 
+@pytest.mark.parametrize("mode", [0, 1])
+def test_dense_cluster_takes_the_generic_search(pk, gpu, oracle, mode):
+    """relation.cu: a candidate run longer than the 128 bits the masked search keeps per run raises the overflow
+    flag and the relation falls back to the generic two-pass search (no hit masks: the union lists are then merged
+    from the index lists).  Neighbour sets and the density sums of both kernel families against the oracle."""
+    rng = np.random.default_rng(3)
+    dp = 0.05
+    lattice = (np.mgrid[0:12, 0:12, 0:12].reshape(3, -1).T + 0.5) * dp
+    blob = 0.27 + 0.05 * rng.random((400, 3))  # 400 particles inside one 0.13-wide cell
+    pos = np.concatenate([lattice, blob])
+    res = {}
+    for name, backend in (("gpu", gpu), ("oracle", oracle)):
+        s = backend.SPHSystem(3, [0, 0, 0], [0.6, 0.6, 0.6], dp)
+        if name == "gpu":
+            s.set_pair_kernel(mode)
+        b = s.add_body("b", len(pos), dp)
+        b.set_fluid(1.0, 10.0)
+        b.set("Position", pos)
+        b.set("VolumetricMeasure", np.full(len(pos), dp ** 3))
+        b.set("Mass", np.full(len(pos), dp ** 3))
+        b.set("Density", np.ones(len(pos)))
+        b.update_cell_list()
+        rel = s.inner(b)
+        rel.update()
+        s.density_summation(rel, None, True)
+        res[name] = (pair_set(rel), field(b, "DensitySummation"))
+    assert res["gpu"][0].shape == res["oracle"][0].shape and np.array_equal(res["gpu"][0], res["oracle"][0])
+    counts = np.bincount(res["gpu"][0][:, 0])
+    assert counts.max() > 400  # the blob's particles see each other: runs far beyond 128 candidates
+    assert rel_l2(res["gpu"][1], res["oracle"][1]) < 1e-12
+
+
 def test_neighbor_sets_periodic(pk, gpu, oracle):
     g, o = both(pk, gpu, oracle, pk.cases.TaylorGreen, dp=0.02)
     pg, po = pair_set(g.inner), pair_set(o.inner)
