@@ -323,7 +323,7 @@ __global__ void __launch_bounds__(128) k_search_mask(int64_t n_src, const typena
                         // (mm - lo < 0: hit, hi - mm < 0: miss; a NaN is 0x7fffffff in fp32, sign clear: undecided)
                         // and shifted into the words by one funnel shift each; candidate t lands on bit m-1-t
                         const float4 *cand = xf_t + j0;
-                        u32 hits = 0u, decided = 0u;
+                        u32 hits = 0u, misses = 0u;
 #pragma unroll 8
                         for (u32 t = 0; t < m; ++t)
                         {
@@ -337,11 +337,11 @@ __global__ void __launch_bounds__(128) k_search_mask(int64_t n_src, const typena
                             }
                             const u32 a = __float_as_uint(mm - pre.lo), b = __float_as_uint(pre.hi - mm);
                             hits = __funnelshift_l(a, hits, 1);
-                            decided = __funnelshift_l(a | b, decided, 1);
+                            misses = __funnelshift_l(b, misses, 1);
                         }
                         const u32 live = m == 32u ? 0xffffffffu : (1u << m) - 1u;
                         word = __brev(hits) >> (32u - m);
-                        todo = ~(__brev(decided) >> (32u - m)) & live;
+                        todo = ~(__brev(hits | misses) >> (32u - m)) & live;
                     }
                     else
                         todo = m == 32u ? 0xffffffffu : (1u << m) - 1u;
