@@ -264,7 +264,7 @@ void sphb200_ctx_destroy(sphb200_ctx *ctx)
             d->release();
         delete b;
     }
-    for (DevBuf *d : {&ctx->scratch_a, &ctx->scratch_b, &ctx->scan_tmp, &ctx->reduce_dev, &ctx->mask_buf, &ctx->subkey_buf})
+    for (DevBuf *d : {&ctx->scratch_a, &ctx->scratch_b, &ctx->scan_tmp, &ctx->reduce_dev, &ctx->subkey_buf})
         d->release();
     if (ctx->reduce_host)
         cudaFreeHost(ctx->reduce_host);

@@ -226,7 +226,7 @@ struct sphb200_ctx
     int pair_kernel = -2; // -2: process default (env SPHB200_TILE), -1 auto, 0 per-particle lists, 1 group-tiled
     std::vector<sphb200_body *> bodies;
     std::vector<sphb200_relation *> relations;
-    sphb::DevBuf scratch_a, scratch_b, scan_tmp, reduce_dev, mask_buf, subkey_buf;
+    sphb::DevBuf scratch_a, scratch_b, scan_tmp, reduce_dev, subkey_buf;
     void *reduce_host = nullptr; // pinned, 64 doubles
 
     sphb200_status fail(sphb200_status s, const std::string &msg)
