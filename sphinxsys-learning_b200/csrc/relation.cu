@@ -223,7 +223,9 @@ __global__ void __launch_bounds__(128) k_search(int64_t n_src, const typename Re
 //   k_search_mask : per particle, per candidate run (the <= 3 cells along the fastest axis of each of the
 //                   3^(D-1) neighbouring cell columns are contiguous particles) a hit bit per candidate,
 //                   kRunWords 32-bit words per run; also count[i] and the slice widths.
-//   k_expand_mask : after the scan of the slice widths, turns the hit bits into the index list.
+//   k_expand_mask : after the scan of the slice widths, turns the hit bits into the index list - only when a
+//                   kernel asks for the list (ensureList); the group-tiled kernels build their union lists from
+//                   the bits themselves (tile.cuh k_union_mask).
 // The second pass of the generic path (another ~474 distance tests per particle in 3-D) is replaced by
 // ~80 bit extractions.  A run longer than 32*kRunWords candidates raises the overflow flag and the host
 // falls back to the generic two-pass search.
