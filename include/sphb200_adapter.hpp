@@ -190,6 +190,15 @@ class SPHBody
         if (n_)
             ck(sphb200_var_upload(body_, name.c_str(), values.data()), "setVariable");
     }
+    // Double-buffered synchronizeToDevice: stageVariable starts the copy of a (pinned) host array on the library's
+    // copy stream while the dynamics already queued keep running; commitStagedVariables swaps the copies in.
+    // The host array must stay untouched in between; update the cell linked list and the relations afterwards.
+    void stageVariable(const std::string &name, const Real *values)
+    {
+        if (n_)
+            ck(sphb200_var_stage(body_, name.c_str(), values), "stageVariable");
+    }
+    void commitStagedVariables() { ck(sphb200_body_commit_staged(body_), "commitStagedVariables"); }
     // getVariableDataByName + synchronizeWithDevice: a host copy in the current particle order
     std::vector<Real> getVariableDataByName(const std::string &name)
     {
