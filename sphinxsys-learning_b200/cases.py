@@ -172,8 +172,11 @@ class DamBreak:
         S.integration_2nd_half(self.inner, self.wall_contact, True, dt)
         self.n_acoustic += 1
 
-    def advection_step(self, sort_interval=100, observer=True):
-        """one outer iteration of dambreak.cpp:159-195; returns (Dt, number of acoustic sub-steps)"""
+    def advection_step(self, sort_interval=100, observer=True, before_configuration=None):
+        """one outer iteration of dambreak.cpp:159-195; returns (Dt, number of acoustic sub-steps).
+        before_configuration(): called between the sub-step loop and the configuration update, where
+        the 2-D main samples its observables (Dambreak.cpp:196-207, i.e. with the previous step's
+        observer configuration)"""
         S, w = self.sys, self.water
         Dt = S.advection_dt(w, self.U_ref)
         S.density_summation(self.inner, self.wall_contact, free_surface=True)
@@ -188,6 +191,8 @@ class DamBreak:
             relaxation += self.dt
             self.time += self.dt
             k += 1
+        if before_configuration is not None:
+            before_configuration()
         self.n_advection += 1
         if sort_interval and self.n_advection % sort_interval == 0 and self.n_advection != 1:
             w.sort()
@@ -280,7 +285,7 @@ class TwistingColumn:
         self.holder_ids = np.nonzero(in_box(pts, [-0.5 * SL, 0, 0], [0.5 * SL, 0.5 * PH, 0.5 * PW]))[0]
         rho0 = 1100.0
         vol = dtype(dp) ** 3
-        self.column = c = self.sys.add_body("Column", n, dp)
+        self.column = c = self.sys.add_body("Column", n, dp, h_ratio=1.15)  # SolidBody: bodies/predefined_bodies.h:44-54
         c.set_elastic(rho0, 1.7e7, 0.45)
         c.set("Position", pts)
         c.set("InitialPosition", pts)

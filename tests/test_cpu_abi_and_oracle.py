@@ -78,12 +78,82 @@ def test_lattice_sizes_and_kernel_kats(pk, oracle):
     assert abs(tg.sys.total_kinetic_energy(tg.water) - 0.25) < 1e-12  # golden sample 0 = 0.25000000000000011
 
 
-def test_oracle_inside_reference_regression_envelopes():
-    """run-level pin of the oracle: same observables the reference's regression tests store"""
+# ------------------------------------------------------------------------------------------------
+# Run-level pin of the oracle: the FULL stored series of every fixture the reference's tests hold for the
+# path (tests/golden), under (a) the north-star strict criterion - every sample within 1 % of the stored
+# runs - where the fixture demonstrably comes from the current classic sources, and (b) the reference's
+# own acceptance test (testResult: DTW distance <= 1.01 x stored, restated in oracle/validate_golden.py)
+# everywhere.  DESIGN.md section 4 holds the per-case findings.
+# ------------------------------------------------------------------------------------------------
+def test_twisting_column_reproduces_the_stored_run_digit_for_digit():
+    """all 3127 stored samples of the free-end observer (6 significant digits in the XML), position and
+    velocity: equal to the fixture's own precision.  (SolidBody smoothing length 1.15 dp,
+    bodies/predefined_bodies.h:44-54 - with 1.3 dp the series is 11 % off after 1200 steps.)"""
     from oracle import validate_golden as vg
-    r = vg.dambreak_2d(3)
-    assert r["max_rel_dev"] < 0.01, r          # north-star run-level criterion: 1 %
-    r = vg.taylor_green(2)
-    assert r["max_rel_dev"] < 0.01, r
-    r = vg.twisting_column(60)
-    assert r["max_rel_dev"] < 0.01, r
+    r = vg.twisting_column(3127)
+    assert r["steps"] == 3126  # the reference's loop also ends after 3126 steps (t >= 0.5)
+    assert r["MyObserver_Position"]["max_rel_dev"] < 2e-6 and r["MyObserver_Position"]["dtw_ok"], r
+    assert r["MyObserver_Velocity"]["max_rel_dev"] < 1e-5 and r["MyObserver_Velocity"]["dtw_ok"], r
+
+
+def test_dambreak_3d_full_series_within_one_percent():
+    """the headline case: all 21 stored energy samples (t = 0..20) within 1 %, the six probe-pressure
+    series (one sample per advection step) under the reference's DTW criterion"""
+    from oracle import validate_golden as vg
+    r = vg.dambreak_3d(21)
+    e = r["WaterBody_TotalMechanicalEnergy"]
+    assert e["snapshots"] == [21, 21] and e["max_rel_dev"] < 0.01 and e["dtw_ok"], r
+    p = r["FluidObserver_Pressure"]
+    assert p["dtw_ok"] and 0.8 * 2180 <= r["advection_steps"] <= 1.2 * 2180, r
+
+
+def test_dambreak_2d_and_taylor_green_pass_the_reference_acceptance_test():
+    """full series (23 / 51 samples) under RegressionTestDynamicTimeWarping::testResult; the strict 1 %
+    window is asserted where it holds (dam break: samples 0-4, Taylor-Green: 0-1)"""
+    from oracle import validate_golden as vg
+    r = vg.dambreak_2d(23)
+    assert r["WaterBody_TotalMechanicalEnergy"]["dtw_ok"] and r["FluidObserver_Pressure"]["dtw_ok"], r
+    assert r["WaterBody_TotalMechanicalEnergy"]["first_sample_over_1pct"] >= 5, r
+    assert abs(r["ours_energy"][0] - 1.0000000000000016) < 1e-13
+    r = vg.taylor_green(51)
+    assert r["WaterBody_TotalKineticEnergy"]["dtw_ok"] and r["WaterBody_MaximumSpeed"]["dtw_ok"], r
+    assert r["WaterBody_TotalKineticEnergy"]["first_sample_over_1pct"] >= 2, r
+
+
+@pytest.mark.xfail(strict=True, reason="fixtures predate the current classic scheme (DESIGN.md section 4): the 2-D dam-break "
+                   "energy file is byte-identical to the CK/SYCL twin's, the Taylor-Green runs were recorded with an "
+                   "un-limited transport-velocity correction; kept visible, not hidden")
+def test_strict_one_percent_on_the_stale_fixtures():
+    from oracle import validate_golden as vg
+    r2 = vg.dambreak_2d(23)
+    rt = vg.taylor_green(51)
+    assert r2["WaterBody_TotalMechanicalEnergy"]["max_rel_dev"] < 0.01 and rt["WaterBody_TotalKineticEnergy"]["max_rel_dev"] < 0.01
+
+
+def test_taylor_green_fixture_vintage_is_reproduced():
+    """oracle/experiments/tg_variants.py: with every switch at the current sources' setting the numpy
+    restatement reproduces liboracle (so the restatement is not the variable); switching ONLY the
+    transport-velocity limiter off (NoLimiter, the pre-TruncatedLinear scheme) moves the t = 0.1 sample
+    from 2.1e-3 to < 1e-4 of the stored 0.20646315402108778 and the maximum speed from 7.8e-3 to < 5e-4"""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "experiments"))
+    import tg_variants as tv
+    from oracle import validate_golden as vg
+    ke_gold, vmax_gold = tv.GOLD[0.1]
+    (_, _, ke, vmax), = tv.sample({}, (0.1,))
+    lib = vg.taylor_green(2)["ours_ke"][1]
+    assert abs(ke - lib) < 1e-12 * lib
+    assert abs(ke - ke_gold) / ke_gold > 1e-3 and abs(vmax - vmax_gold) / vmax_gold > 5e-3
+    (_, _, ke, vmax), = tv.sample({"tvc": "plain"}, (0.1,))
+    assert abs(ke - ke_gold) / ke_gold < 1e-4 and abs(vmax - vmax_gold) / vmax_gold < 5e-4
+
+
+def test_reference_dtw_restatement_known_answers():
+    """dtw_reference against hand-evaluated cases of dynamic_time_warping_method.hpp:16-55"""
+    from oracle import validate_golden as vg
+    a = np.arange(12.0)
+    assert vg.dtw_reference(a, a) == 0.0
+    assert vg.dtw_reference(a, a + 1.0) == 2.0     # band edge restarts the accumulation: far below the true 11 + ...
+    assert vg.dtw_reference(a, np.arange(20.0)) == float("inf")  # length changed by > 20 %: the reference exits
+    v = np.stack([a, a], 1)
+    assert vg.dtw_reference(v, v) == 0.0
