@@ -74,11 +74,21 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def cpu_reference_run(dp, steps, warmup):
     """the reference algorithm on the host cores: the CPU restatement (oracle, kind "port") - the TBB
-    build of the reference cannot be compiled in this image (no Eigen/TBB/Boost/Simbody)."""
+    build of the reference cannot be compiled in this image (no Eigen/TBB/Boost/Simbody).  Runs on every
+    core this process may use, whatever OMP_NUM_THREADS the launcher exported (torch.distributed.run sets 1)."""
     pk = importlib.import_module("sphinxsys-learning_b200")
+    os.environ["OMP_NUM_THREADS"] = str(host_cores())
     from oracle import binding as oracle
+    oracle.load().orc_set_num_threads(host_cores())
     c = pk.cases.DamBreak(oracle, ndim=3, dp=dp, real_bytes=8, with_observer=False)
     for _ in range(warmup):
         c.advection_step()
@@ -253,6 +263,8 @@ def main():
     ap.add_argument("--cpu-dp", type=float, default=1.0 / 96.0, help="spacing of the bounded CPU-baseline sample (1/96 -> 884 736 fluid particles)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-disordered", action="store_true", help="skip the jittered-state leg")
+    ap.add_argument("--no-fp32", action="store_true", help="skip the fp32 build's legs (extra key \"fp32\")")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -262,11 +274,13 @@ def main():
     if a.impl == "reference":
         if rank != 0:
             return
-        base, ms = cpu_reference_run(a.cpu_dp, max(a.steps, 1), 1)
+        base, ms = cpu_reference_run(a.cpu_dp, max(a.steps, 1), a.warmup)
         emit(json.dumps({"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": a.gpus,
-                          "steps": a.steps, "warmup": 1, "ms_per_step": ms * 1e3, "higher_is_better": True, "scaling": "weak",
+                          "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms * 1e3, "higher_is_better": True, "scaling": "weak",
                           "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                          "config": {"workload": "test_3d_dambreak lattice, bounded CPU sample", "dp": a.cpu_dp},
+                          "config": {"workload": "test_3d_dambreak lattice, bounded CPU sample (host RAM bounds the stored-neighbourhood "
+                                                 "algorithm to ~2 M particles; particle-steps/s of this O(N) algorithm does not depend on N)",
+                                     "dp": a.cpu_dp, "cores": base["cores"]},
                           "cpu_baseline": base,
                           "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
         return
@@ -288,87 +302,98 @@ def main():
     if world > 1:
         return slab_main(a, pk, stream, rank, world, local_rank, warmup)
 
+    out = single_gpu(a, pk, stream, local_rank, warmup, a.real, rank == 0 and not a.no_cpu_baseline)
+    if not a.no_fp32 and a.real == 8:
+        # the same workload and legs in the fp32 build (the reference's SPHINXSYS_USE_FLOAT), reported as an extra key
+        f32 = single_gpu(a, pk, stream, local_rank, warmup, 4, False, short=True)
+        out["fp32"] = {k: f32[k] for k in ("value", "ms_per_step", "roofline", "step_roofline_frac", "e2e", "value_disordered")}
+    emit(json.dumps(out))
+
+
+def single_gpu(a, pk, stream, device, warmup, R, with_cpu, short=False):
+    import torch
     # ---- build the case ----
     t_build = time.perf_counter()
-    case = pk.cases.DamBreak(pk.host, ndim=3, dp=a.dp, real_bytes=a.real, with_observer=True, device=local_rank,
+    case = pk.cases.DamBreak(pk.host, ndim=3, dp=a.dp, real_bytes=R, with_observer=True, device=device,
                              stream=stream.cuda_stream)
     S, w = case.sys, case.water
     t_build = time.perf_counter() - t_build
     n_f, n_w = w.n, case.wall.n
+    steps = max(3, a.steps // 3) if short else a.steps
+    evolving = ("Position", "Velocity", "Density", "Pressure", "DensityChangeRate", "Force", "ForcePrior", "Mass",
+                "VolumetricMeasure", "PreviousGravityForce")
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
+    def timed_steps(fn, k):
         torch.cuda.synchronize()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0, sub0 = S.launches, case.n_acoustic
+        t0 = time.perf_counter()
+        ev0.record(stream)
+        for _ in range(k):
+            fn()
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        return ev0.elapsed_time(ev1), (time.perf_counter() - t0) * 1e3, case.n_acoustic - sub0, S.launches - l0
+
+    def kernel_ms(fn, reps=5):
+        """CUDA-event time of one call of fn on the launching stream; the fields fn accumulates into are restored"""
+        keep = {nm: w.get(nm) for nm in ("DensityChangeRate", "Force", "Density", "Position", "Velocity", "Pressure")}
+        fn()
+        torch.cuda.synchronize()
+        k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        k0.record(stream)
+        for _ in range(reps):
+            fn()
+        k1.record(stream)
+        torch.cuda.synchronize()
+        for nm, v in keep.items():
+            w.set(nm, v)
+        return k0.elapsed_time(k1) / reps
 
     # ---- `value`: state resident in HBM ---------------------------------------------------------
     for _ in range(warmup):
         case.advection_step()
-    barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
-    launches0, sub0 = S.launches, case.n_acoustic
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record(stream)
-    for _ in range(a.steps):
-        case.advection_step()
-    ev1.record(stream)
-    barrier()
-    clocks = sampler.stop() if sampler else None
-    ms = ev0.elapsed_time(ev1)
-    sub = case.n_acoustic - sub0
-    launches = S.launches - launches0
-    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
-    value = world * n_f * sub / (ms_max * 1e-3)
+    sampler = ClockSampler(device)
+    ms, _, sub, launches = timed_steps(case.advection_step, steps)
+    clocks = sampler.stop()
+    value = n_f * sub / (ms * 1e-3)
 
     # ---- roofline of the dominant kernel (Integration2ndHalf: one launch per call) ---------------
-    pairs_in, pairs_w = case.inner.neighbor_counts()[1], case.wall_contact.neighbor_counts()[1]
-    R = a.real
-    fields_B = 20 * R  # K3 of SURVEY §8d: 160 B fp64 / 80 B fp32 per particle
-    alg_bytes = n_f * fields_B + 4 * (pairs_in + pairs_w)
-    reps = 5
-    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    S.integration_2nd_half(case.inner, case.wall_contact, True, 0.0)
-    torch.cuda.synchronize()
-    k0.record(stream)
-    for _ in range(reps):
-        S.integration_2nd_half(case.inner, case.wall_contact, True, 0.0)
-    k1.record(stream)
-    torch.cuda.synchronize()
-    k_ms = k0.elapsed_time(k1) / reps
     peak, peak_src = peaks()
-    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    traffic = None
-    try:  # DRAM bytes of this kernel at this size from the committed ncu --set full capture (profiles/traffic.json)
+
+    def roofline_now():
+        pairs_in, pairs_w = case.inner.neighbor_counts()[1], case.wall_contact.neighbor_counts()[1]
+        alg_bytes = n_f * 20 * R + 4 * (pairs_in + pairs_w)  # K3 of SURVEY 8d: 160 B fp64 / 80 B fp32 per particle + list
+        k3 = kernel_ms(lambda: S.integration_2nd_half(case.inner, case.wall_contact, True, 0.0))
+        k12 = kernel_ms(lambda: S.integration_1st_half(case.inner, case.wall_contact, True, 0.0))
+        achieved = alg_bytes / (k3 * 1e-3) / 1e9
+        st = case.inner.stats()
+        return {"bound": "hbm", "kernel": "Integration2ndHalf inner+wall, fused init/update (k_second_half_tile; wall sums from k_second_half_wall)",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "kernel_ms": k3, "first_half_ms": k12, "algorithmic_bytes_per_launch": alg_bytes,
+                "pairs_per_particle": (pairs_in + pairs_w) / n_f,
+                "union_slots_per_group": st["union_entries"] / max(st["union_groups"], 1), "group_size": st["group_size"],
+                "masked_search": st["masked_search"] and case.wall_contact.stats()["masked_search"]}
+
+    roofline = roofline_now()
+    try:  # DRAM bytes of this kernel at this size from the committed ncu --set full capture (profiles/traffic.json),
+        # keyed by kernel name and N - a number from the capture, not from this run
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
             tj = json.load(fh)
         key = f"k_second_half_tile<3,double,2>@{n_f}"
         if R == 8 and key in tj:
-            traffic = tj[key]["dram_bytes_per_launch"]
+            roofline["traffic"] = tj[key]["dram_bytes_per_launch"]
+            roofline["traffic_source"] = "profiles/traffic.json (ncu --set full capture of this kernel at this N, not this run)"
     except Exception:
-        traffic = None
-    roofline = {"bound": "hbm", "kernel": "Integration2ndHalf inner+wall, fused init/update (k_second_half_tile; wall sums from k_second_half_wall)",
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "peak_source": peak_src, "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg_bytes,
-                "pairs_per_particle": (pairs_in + pairs_w) / n_f}
-    a_step = 56 * R + 2 * 4 * (pairs_in + pairs_w) / n_f  # SURVEY §8d A_step: 448/224 B fields + 2 list reads
-    step_frac = a_step * value / world / 1e9 / peak
+        pass
+    a_step = 56 * R + 2 * 4 * roofline["pairs_per_particle"]  # SURVEY 8d A_step: 448/224 B fields + 2 list reads
+    step_frac = a_step * value / 1e9 / peak
 
     # ---- `e2e`: host buffers in, observables out, every step ------------------------------------
     e2e = None
     if not a.no_e2e:
-        names = [n for n in ("Position", "Velocity", "Density", "Pressure", "DensityChangeRate", "Force", "ForcePrior",
-                             "Mass", "VolumetricMeasure")]
-        host = {}
-        for nm in names:
-            arr = w.get(nm)
-            pinned = torch.from_numpy(arr).pin_memory()
-            host[nm] = pinned
+        host = {nm: torch.from_numpy(w.get(nm)).pin_memory() for nm in evolving}
         h2d = sum(v.numel() * v.element_size() for v in host.values())
-        lib = S.lib
-        import ctypes as C
 
         def stage_inputs():
             for nm, ten in host.items():
@@ -386,49 +411,76 @@ def main():
             case.update_configuration()
             case.advection_step()
             # the step's result: the observables the reference's regression tests record (energy, probe pressures)
-            e = case.mechanical_energy()
-            p = case.probe_pressure()
-            return e, p
+            return case.mechanical_energy(), case.probe_pressure()
 
         stage_inputs()
         e2e_step()
-        barrier()
-        sub0 = case.n_acoustic
+        ms_e, wall_e, sub_e, _ = timed_steps(e2e_step, steps)
+        # output-interval leg: what the reference moves when it writes a state (BodyStatesRecordingToVtp: Position,
+        # Velocity, Density, Pressure) - asynchronous device -> pinned host copies, timed on their own
+        out_names = ("Position", "Velocity", "Density", "Pressure")
+        torch.cuda.synchronize()
         t0 = time.perf_counter()
-        ev0.record(stream)
-        for _ in range(a.steps):
-            e2e_step()
-        ev1.record(stream)
-        barrier()
-        ms_e = max(ev0.elapsed_time(ev1), (time.perf_counter() - t0) * 1e3)
-        t = torch.tensor([ms_e], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        sub_e = case.n_acoustic - sub0
-        e2e = {"value": world * n_f * sub_e / (float(t.item()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(8 + 8 * 6 + 8 * (sub_e // max(a.steps, 1) + 1)),
-               "note": "every step takes the evolving fluid state from pinned host arrays (sphb200_var_stage + "
-                       "sphb200_body_commit_staged: double-buffered, the copy of step k+1's inputs runs on a copy stream "
-                       "while step k computes; all copies lie inside the timed region, whose end waits for the device), "
+        for nm in out_names:
+            w.fetch_async(nm, host[nm].data_ptr())
+        S.fetch_wait()
+        out_ms = (time.perf_counter() - t0) * 1e3
+        out_bytes = sum(host[nm].numel() * host[nm].element_size() for nm in out_names)
+        e2e = {"value": n_f * sub_e / (max(ms_e, wall_e) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(8 + 8 * 6 + 8 * (sub_e // max(steps, 1) + 1)),
+               "output_interval_leg": {"ms": out_ms, "d2h_bytes": int(out_bytes), "GBps": out_bytes / out_ms / 1e6,
+                                       "what": "Position, Velocity, Density, Pressure to pinned host memory (sphb200_var_fetch_async + "
+                                               "sphb200_ctx_fetch_wait), once per output interval in the reference, not per step"},
+               "note": "every timed step uploads the whole evolving fluid state (10 variables) from pinned host arrays "
+                       "(sphb200_var_stage + sphb200_body_commit_staged: double-buffered, the copy of step k+1's inputs runs on a "
+                       "copy stream while step k computes; all copies lie inside the timed region, whose end waits for the device), "
                        "rebuilds cell list + relations, runs one advection step and reads back the step's results: total "
-                       "mechanical energy, the 6 probe pressures and the dt values"}
+                       "mechanical energy, the 6 probe pressures and the dt values.  The host arrays hold the state captured "
+                       "after the resident leg and are not refreshed, so every timed step integrates the same state; updated "
+                       "particle state crosses back only at output intervals (output_interval_leg), as in the reference"}
+
+    # ---- disordered state: SURVEY 8d jitter (U(-0.2 dp, 0.2 dp), seed 12345) + seeded velocities -------------------
+    disordered = None
+    if not a.no_disordered:
+        rng = np.random.default_rng(12345)
+        dtype = np.float64 if R == 8 else np.float32
+        oid, _ = w.ids()
+        pos = w.get("Position")
+        # keyed by original id, so every build of the library sees the same state
+        jit = (rng.uniform(-0.2, 0.2, size=pos.shape) * a.dp).astype(dtype)
+        vel = rng.normal(0.0, 0.1 * case.U_ref, size=pos.shape).astype(dtype)
+        w.set("Position", pos + jit[oid])
+        w.set("Velocity", vel[oid])
+        w.set("Density", np.full(n_f, case.rho0, dtype))
+        for nm in ("DensityChangeRate", "Pressure"):
+            w.set(nm, np.zeros(n_f, dtype))
+        w.set("Force", np.zeros_like(pos))
+        w.update_cell_list()
+        case.update_configuration()
+        case.dt = 0.0
+        for _ in range(2):
+            case.advection_step()
+        ms_d, _, sub_d, _ = timed_steps(case.advection_step, steps)
+        rd = roofline_now()
+        disordered = {"value": n_f * sub_d / (ms_d * 1e-3), "ms_per_step": ms_d / steps, "acoustic_substeps": sub_d,
+                      "kernel_ms": rd["kernel_ms"], "first_half_ms": rd["first_half_ms"], "frac": rd["frac"],
+                      "pairs_per_particle": rd["pairs_per_particle"], "union_slots_per_group": rd["union_slots_per_group"],
+                      "masked_search": rd["masked_search"],
+                      "state": "lattice + U(-0.2 dp, 0.2 dp) jitter (seed 12345), velocities N(0, 0.1 U_ref), 2 untimed steps first"}
 
     cpu_base = None
-    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+    if with_cpu:
         cpu_base, _ = cpu_reference_run(a.cpu_dp, 16, 1)  # ~11 s of CPU work on 16 cores
 
-    if rank == 0:
-        out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": warmup,
-               "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-               "dtype": "f64" if R == 8 else "f32", "data": "synthetic",
-               "config": {"workload": f"test_3d_dambreak lattice dp={a.dp:.6g}: {n_f} fluid + {n_w} wall particles per GPU",
-                          "acoustic_substeps": sub, "advection_steps": a.steps, "l2": "inputs larger than L2",
-                          "parallelism": "1 slab per GPU" if world > 1 else "single GPU", "build_seconds": round(t_build, 1)},
-               "roofline": roofline, "step_roofline_frac": step_frac, "a_step_bytes": a_step,
-               "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
-        emit(json.dumps(out))
-    if world > 1:
-        dist.destroy_process_group()
+    return {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64" if R == 8 else "f32", "data": "synthetic",
+            "config": {"workload": f"test_3d_dambreak lattice dp={a.dp:.6g}: {n_f} fluid + {n_w} wall particles per GPU",
+                       "acoustic_substeps": sub, "advection_steps": steps, "l2": "inputs larger than L2",
+                       "parallelism": "single GPU", "build_seconds": round(t_build, 1)},
+            "roofline": roofline, "step_roofline_frac": step_frac, "a_step_bytes": a_step,
+            "value_disordered": disordered["value"] if disordered else None, "disordered": disordered,
+            "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
 
 
 if __name__ == "__main__":

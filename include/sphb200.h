@@ -84,13 +84,28 @@ sphb200_status sphb200_var_to_host(sphb200_body *b, const char *name);
 sphb200_status sphb200_var_upload(sphb200_body *b, const char *name, const void *src);
 sphb200_status sphb200_var_download(sphb200_body *b, const char *name, void *dst);
 /* Double-buffered upload.  var_stage starts an asynchronous copy of a host buffer (n*width Reals; pinned memory
- * for a real overlap, and untouched until the commit) into a staging mirror on the context's copy stream - the
- * dynamics queued on the compute stream keep running on the current mirrors.  body_commit_staged makes the compute
- * stream wait for those copies and swaps every staged mirror in (like var_upload, the variables count as rewritten:
- * call cell_list_update afterwards).  The SYCL twin is the queue-ordered copy of
- * src_sycl/shared/common/sphinxsys_variable_sycl.hpp:35-87, which the host thread does not wait for either. */
+ * for a real overlap) into a staging mirror on the context's copy stream - the dynamics queued on the compute
+ * stream keep running on the current mirrors.  The host buffer stays RESERVED until sphb200_ctx_stage_wait (or
+ * sphb200_ctx_synchronize) returns: body_commit_staged only orders the compute stream after the copies, it does not
+ * block the host.  body_commit_staged swaps every staged mirror in (like var_upload, the variables count as
+ * rewritten: call cell_list_update afterwards).  If the body was re-sorted (cell_list_update) between var_stage and
+ * the commit, the staged rows are in another particle order than the resident ones: the commit then requires EVERY
+ * evolving variable to be staged (status INVALID otherwise), the staged row order becomes the body's order,
+ * OriginalID/SortedID restart from the identity (sphb200_ids_from_host restores saved ones) and the cell list and
+ * relations are invalidated - the semantics of a reload (io_system/io_base.cpp:67-97, Dambreak.cpp:132-138).
+ * The SYCL twin is the queue-ordered copy of src_sycl/shared/common/sphinxsys_variable_sycl.hpp:35-87, which the
+ * host thread does not wait for either. */
 sphb200_status sphb200_var_stage(sphb200_body *b, const char *name, const void *src);
 sphb200_status sphb200_body_commit_staged(sphb200_body *b);
+sphb200_status sphb200_ctx_stage_wait(sphb200_ctx *ctx);
+/* Asynchronous, double-buffered device -> host read for the output / restart path
+ * (BaseVariable::prepareForOutput(ParallelDevicePolicy), common/sphinxsys_variable.h:350-356;
+ * BodyStatesRecording / RestartIO::writeToFile, io_system/io_base.cpp:67-97): a device-side snapshot is taken in
+ * stream order, the copy to dst (n*width Reals, pinned for a real overlap) runs on a separate stream while the
+ * dynamics continue; rows are in the body's order at the time of the call.  ctx_fetch_wait blocks the host until
+ * every fetch issued so far has landed. */
+sphb200_status sphb200_var_fetch_async(sphb200_body *b, const char *name, void *dst);
+sphb200_status sphb200_ctx_fetch_wait(sphb200_ctx *ctx);
 /* DelegatedData(par_device): raw device pointer, valid until the next cell_list_update of b */
 sphb200_status sphb200_var_device_ptr(sphb200_body *b, const char *name, void **out);
 /* Reals per particle of a registered variable (DiscreteVariable<T>: sizeof(T)/sizeof(Real),
@@ -98,6 +113,9 @@ sphb200_status sphb200_var_device_ptr(sphb200_body *b, const char *name, void **
 sphb200_status sphb200_var_width(sphb200_body *b, const char *name, int *width);
 /* OriginalID / SortedID (particles/base_particles.cpp:33-38), widened to int64 */
 sphb200_status sphb200_ids_to_host(sphb200_body *b, int64_t *original_id, int64_t *sorted_id);
+/* restores OriginalID (a permutation of 0..n-1, current row order) after a reload and rebuilds SortedID
+ * (particle_sorting.cpp:55-58; the reference's restart file carries OriginalID, base_particles.cpp:33-37) */
+sphb200_status sphb200_ids_from_host(sphb200_body *b, const int64_t *original_id);
 
 /* ---- spatial search ------------------------------------------------------------------------ */
 /* RealBody::updateCellLinkedList (bodies/base_body.cpp:113-116 → meshes/cell_linked_list.cpp:84-101;
@@ -124,6 +142,10 @@ sphb200_status sphb200_relation_contact_create(sphb200_body *b, sphb200_body *co
 sphb200_status sphb200_relation_update(sphb200_relation *r);
 /* parity/debug: counts[n] and flat neighbour indices (list order) of target k; returns the total */
 sphb200_status sphb200_relation_neighbors(sphb200_relation *r, int k, int32_t *counts, int64_t *j_out, int64_t *total);
+/* measurement: out8 = {accepted pairs, 1 if the single-pass masked search held (0: a candidate run overflowed its
+ * mask words or the target is periodic -> generic two-pass search), 1 if the u32 index list is materialised,
+ * union-list entries, union groups, particles per group (0 until a group-tiled kernel built it), n_source, build id} */
+sphb200_status sphb200_relation_stats(sphb200_relation *r, int k, double *out8);
 
 /* ---- weakly compressible fluid dynamics ---------------------------------------------------- */
 /* DensitySummation<Inner<>|Inner<FreeSurface>> (+Contact<>) interaction+update
@@ -196,7 +218,7 @@ sphb200_status sphb200_body_keep_range(sphb200_body *b, int64_t begin, int64_t e
 /* index of the first particle (cell-sorted order) whose cell page along axis 0 is >= page; needs a valid
  * cell list.  page <= 0 gives 0, page >= number of pages gives n */
 sphb200_status sphb200_body_page_begin(sphb200_body *b, int page, int64_t *out);
-/* the packed gather records of the acoustic sub-step (Rec8 = 8 Reals per particle {x,y,z,Vol|p,vx,vy,vz},
+/* the packed gather records of the acoustic sub-step (Rec8 = 8 Reals per particle {x,y,z,p|Vol,vx,vy,vz},
  * which = 0: rec_a written by the 1st-half initialization, 1: rec_b written by the 1st-half update).  A
  * slab run overwrites the records of its halo copies with the owner's between the stages. */
 sphb200_status sphb200_body_record_ptr(sphb200_body *b, int which, void **out);

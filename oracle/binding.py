@@ -47,7 +47,7 @@ def load():
         "orc_maximum_speed": (d, [vp, i]), "orc_observe": (None, [vp, i, cp, i, dp]),
         "orc_correction_matrix": (None, [vp, i]), "orc_solid_1st_half": (None, [vp, i, i, d]),
         "orc_solid_2nd_half": (None, [vp, i, d]), "orc_solid_constrain": (None, [vp, i, lp, l]),
-        "orc_solid_dt": (d, [vp, i, d]), "orc_num_threads": (i, []),
+        "orc_solid_dt": (d, [vp, i, d]), "orc_num_threads": (i, []), "orc_set_num_threads": (i, [i]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

@@ -359,4 +359,16 @@ int orc_num_threads()
     return 1;
 #endif
 }
+// the bench's CPU legs run on every host core whatever OMP_NUM_THREADS the launcher exported
+// (torch.distributed.run sets it to 1): returns the thread count in effect afterwards
+int orc_set_num_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0)
+        omp_set_num_threads(n);
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
 } // extern "C"

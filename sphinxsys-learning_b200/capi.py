@@ -46,6 +46,10 @@ SIGNATURES = {
     "sphb200_var_download": (_i, [_vp, _cp, _vp]),
     "sphb200_var_stage": (_i, [_vp, _cp, _vp]),
     "sphb200_body_commit_staged": (_i, [_vp]),
+    "sphb200_ctx_stage_wait": (_i, [_vp]),
+    "sphb200_var_fetch_async": (_i, [_vp, _cp, _vp]),
+    "sphb200_ctx_fetch_wait": (_i, [_vp]),
+    "sphb200_ids_from_host": (_i, [_vp, _i64p]),
     "sphb200_var_device_ptr": (_i, [_vp, _cp, _vpp]),
     "sphb200_var_width": (_i, [_vp, _cp, C.POINTER(C.c_int)]),
     "sphb200_ids_to_host": (_i, [_vp, _i64p, _i64p]),
@@ -57,6 +61,7 @@ SIGNATURES = {
     "sphb200_relation_contact_create": (_i, [_vp, _vpp, _i, _vpp]),
     "sphb200_relation_update": (_i, [_vp]),
     "sphb200_relation_neighbors": (_i, [_vp, _i, C.POINTER(C.c_int32), _i64p, _i64p]),
+    "sphb200_relation_stats": (_i, [_vp, _i, _dp]),
     "sphb200_density_summation": (_i, [_vp, _vp, _i]),
     "sphb200_integration_1st_half": (_i, [_vp, _vp, _i, _d]),
     "sphb200_integration_2nd_half": (_i, [_vp, _vp, _i, _d]),

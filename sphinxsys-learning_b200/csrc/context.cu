@@ -4,6 +4,7 @@
 // BaseParticles' variable registry (particles/base_particles.h:119-162) and the device delegation of
 // DiscreteVariable (common/sphinxsys_variable.h:179-190).
 #include "internal.cuh"
+#include <algorithm>
 
 using namespace sphb;
 
@@ -456,7 +457,24 @@ sphb200_status sphb200_var_stage(sphb200_body *b, const char *name, const void *
     SPHB_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->mirrors_free, 0));
     SPHB_CUDA(ctx, cudaMemcpyAsync(v->stage.p, src, bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
     v->staged_n = b->n;
+    v->staged_stamp = b->config_stamp;
     return SPHB200_OK;
+}
+// blocks the host until every var_stage copy issued so far has left its host buffer
+sphb200_status sphb200_ctx_stage_wait(sphb200_ctx *ctx)
+{
+    if (!ctx)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (ctx->copy_stream)
+        SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
+    return SPHB200_OK;
+}
+__global__ void k_iota_ids(u32 *__restrict__ a, u32 *__restrict__ b, int64_t n)
+{
+    int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n)
+        a[i] = b[i] = u32(i);
 }
 sphb200_status sphb200_body_commit_staged(sphb200_body *b)
 {
@@ -464,16 +482,38 @@ sphb200_status sphb200_body_commit_staged(sphb200_body *b)
         return SPHB200_ERR_INVALID;
     sphb200_ctx *ctx = b->ctx;
     cudaSetDevice(ctx->device);
-    bool any = false;
+    bool any = false, reordered = false;
     for (auto &kv : b->vars)
         if (kv.second->staged_n >= 0)
         {
             if (kv.second->staged_n != b->n)
                 return ctx->fail(SPHB200_ERR_INVALID, "commit_staged: body '" + b->name + "' was resized after var_stage of '" + kv.first + "'");
             any = true;
+            reordered = reordered || kv.second->staged_stamp != b->config_stamp;
         }
     if (!any)
         return SPHB200_OK;
+    if (reordered)
+    {
+        // a cell_list_update ran between var_stage and this commit: the rows of the resident variables are in another
+        // particle order than the staged rows.  Swapping in a subset would silently mix the two, so the staged set must
+        // cover every evolving variable; the staged (host) row order then DEFINES the body's order, as a reload does
+        // (io_base.cpp:67-97 readFromFile + Dambreak.cpp:132-138): ids restart from the identity (sphb200_ids_from_host
+        // restores saved ones) and the cell list / configurations must be rebuilt before the next interaction.
+        for (auto &kv : b->vars)
+            if (kv.second->evolving && kv.second->staged_n < 0)
+                return ctx->fail(SPHB200_ERR_INVALID, "commit_staged: body '" + b->name + "' was re-sorted after var_stage; every evolving "
+                                                      "variable must be staged then, '" + kv.first + "' was not");
+        if (b->n > 0)
+        {
+            k_iota_ids<<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(static_cast<u32 *>(b->original_id.p), static_cast<u32 *>(b->sorted_id.p), b->n);
+            SPHB_LAUNCH_CHECK(ctx);
+        }
+        b->cell_list_valid = false;
+        for (sphb200_relation *r : ctx->relations)
+            if (r->body == b || std::find(r->targets.begin(), r->targets.end(), b) != r->targets.end())
+                r->valid = false;
+    }
     SPHB_CUDA(ctx, cudaEventRecord(ctx->copy_done, ctx->copy_stream));
     SPHB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->copy_done, 0));
     for (auto &kv : b->vars)
@@ -501,6 +541,54 @@ sphb200_status sphb200_var_download(sphb200_body *b, const char *name, void *dst
     size_t bytes = size_t(b->n) * size_t(v->width) * size_t(ctx->real_bytes);
     SPHB_CUDA(ctx, cudaMemcpyAsync(dst, v->dev.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return SPHB200_OK;
+}
+// Asynchronous, double-buffered device -> host read of a variable (the output / restart path:
+// BaseVariable::prepareForOutput(ParallelDevicePolicy), sphinxsys_variable.h:350-356 -> synchronizeWithDevice):
+// a device-side snapshot is taken in stream order (so later kernels and re-sorts do not disturb it), then copied to
+// dst on a separate stream while the compute stream goes on.  dst (pinned for a truly asynchronous copy) holds the
+// rows in the body's CURRENT order once sphb200_ctx_fetch_wait returns.
+sphb200_status sphb200_var_fetch_async(sphb200_body *b, const char *name, void *dst)
+{
+    if (!b || !name || !dst)
+        return SPHB200_ERR_INVALID;
+    sphb200_ctx *ctx = b->ctx;
+    Var *v = b->find(name);
+    if (!v)
+        return ctx->fail(SPHB200_ERR_NOT_FOUND, std::string("variable '") + name + "' is not registered");
+    cudaSetDevice(ctx->device);
+    if (!ctx->fetch_stream)
+    {
+        SPHB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->fetch_stream, cudaStreamNonBlocking));
+        SPHB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->fetch_ready, cudaEventDisableTiming));
+        SPHB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->fetch_done, cudaEventDisableTiming));
+        SPHB_CUDA(ctx, cudaEventRecord(ctx->fetch_done, ctx->fetch_stream));
+    }
+    const size_t bytes = size_t(b->n) * size_t(v->width) * size_t(ctx->real_bytes);
+    if (bytes == 0)
+        return SPHB200_OK;
+    if (v->fetch.bytes < bytes)
+    {
+        SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->fetch_stream));
+        v->fetch.release();
+        SPHB_CUDA(ctx, v->fetch.ensure(bytes));
+    }
+    // the snapshot may be overwritten only after the previous copy out of it has finished
+    SPHB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->fetch_done, 0));
+    SPHB_CUDA(ctx, cudaMemcpyAsync(v->fetch.p, v->dev.p, bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+    SPHB_CUDA(ctx, cudaEventRecord(ctx->fetch_ready, ctx->stream));
+    SPHB_CUDA(ctx, cudaStreamWaitEvent(ctx->fetch_stream, ctx->fetch_ready, 0));
+    SPHB_CUDA(ctx, cudaMemcpyAsync(dst, v->fetch.p, bytes, cudaMemcpyDeviceToHost, ctx->fetch_stream));
+    SPHB_CUDA(ctx, cudaEventRecord(ctx->fetch_done, ctx->fetch_stream));
+    return SPHB200_OK;
+}
+sphb200_status sphb200_ctx_fetch_wait(sphb200_ctx *ctx)
+{
+    if (!ctx)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (ctx->fetch_stream)
+        SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->fetch_stream));
     return SPHB200_OK;
 }
 sphb200_status sphb200_var_to_device(sphb200_body *b, const char *name)
@@ -546,6 +634,41 @@ sphb200_status sphb200_var_width(sphb200_body *b, const char *name, int *width)
     if (!v)
         return b->ctx->fail(SPHB200_ERR_NOT_FOUND, std::string("variable '") + name + "' is not registered");
     *width = v->width;
+    return SPHB200_OK;
+}
+
+__global__ void k_sorted_from_original(const u32 *__restrict__ oid, u32 *__restrict__ sid, int64_t n)
+{
+    int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n)
+        sid[oid[i]] = u32(i); // particle_sorting.cpp:55-58 UpdateSortedID
+}
+// restores OriginalID after a reload (the reference's restart file carries it as an evolving variable,
+// base_particles.cpp:33-37); SortedID is rebuilt.  original_id must be a permutation of 0..n-1.
+sphb200_status sphb200_ids_from_host(sphb200_body *b, const int64_t *original_id)
+{
+    if (!b || !original_id)
+        return SPHB200_ERR_INVALID;
+    sphb200_ctx *ctx = b->ctx;
+    cudaSetDevice(ctx->device);
+    std::vector<u32> tmp(static_cast<size_t>(b->n));
+    std::vector<bool> seen(static_cast<size_t>(b->n), false);
+    for (int64_t i = 0; i < b->n; ++i)
+    {
+        const int64_t o = original_id[i];
+        if (o < 0 || o >= b->n || seen[size_t(o)])
+            return ctx->fail(SPHB200_ERR_INVALID, "ids_from_host: original_id is not a permutation of 0..n-1");
+        seen[size_t(o)] = true;
+        tmp[size_t(i)] = u32(o);
+    }
+    if (b->n > 0)
+    {
+        SPHB_CUDA(ctx, cudaMemcpyAsync(b->original_id.p, tmp.data(), size_t(b->n) * 4, cudaMemcpyHostToDevice, ctx->stream));
+        k_sorted_from_original<<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(static_cast<const u32 *>(b->original_id.p),
+                                                                          static_cast<u32 *>(b->sorted_id.p), b->n);
+        SPHB_LAUNCH_CHECK(ctx);
+        SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
     return SPHB200_OK;
 }
 

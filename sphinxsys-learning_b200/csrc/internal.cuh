@@ -210,6 +210,8 @@ struct Var
     DevBuf alt; // destination of the next cell-order gather (swapped with dev; no allocation per sort)
     DevBuf stage;          // target of var_stage, swapped with dev by body_commit_staged
     int64_t staged_n = -1; // particles the staged copy holds, -1: nothing staged
+    uint64_t staged_stamp = 0; // body.config_stamp when var_stage was called
+    DevBuf fetch;          // device-side snapshot var_fetch_async copies to the host from
 };
 } // namespace sphb
 
@@ -221,6 +223,8 @@ struct sphb200_ctx
     bool owns_stream = true;
     cudaStream_t copy_stream = nullptr; // var_stage copies (created on first use)
     cudaEvent_t copy_done = nullptr, mirrors_free = nullptr;
+    cudaStream_t fetch_stream = nullptr; // var_fetch_async copies (created on first use)
+    cudaEvent_t fetch_ready = nullptr, fetch_done = nullptr;
     std::string error;
     int64_t launches = 0;
     int pair_kernel = -2; // -2: process default (env SPHB200_TILE), -1 auto, 0 per-particle lists, 1 group-tiled

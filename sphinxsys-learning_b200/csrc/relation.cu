@@ -826,4 +826,23 @@ sphb200_status sphb200_relation_neighbors(sphb200_relation *r, int k, int32_t *c
     }
     return SPHB200_OK;
 }
+
+sphb200_status sphb200_relation_stats(sphb200_relation *r, int k, double *out8)
+{
+    if (!r || !out8 || k < 0 || k >= int(r->lists.size()))
+        return SPHB200_ERR_INVALID;
+    if (!r->valid)
+        return r->ctx->fail(SPHB200_ERR_INVALID, "relation_stats: relation has not been updated");
+    const NeighborList &L = r->lists[size_t(k)];
+    const bool uni = L.uni.build_id == L.build_id && L.uni.n_groups > 0;
+    out8[0] = double(L.total_pairs);
+    out8[1] = L.has_mask ? 1.0 : 0.0;
+    out8[2] = L.expanded ? 1.0 : 0.0;
+    out8[3] = uni ? double(L.uni.total_entries) : 0.0;
+    out8[4] = uni ? double(L.uni.n_groups) : 0.0;
+    out8[5] = uni ? double(L.uni.G) : 0.0;
+    out8[6] = double(r->body->n);
+    out8[7] = double(L.build_id);
+    return SPHB200_OK;
+}
 } // extern "C"

@@ -69,6 +69,12 @@ class SPHSystem:
     def synchronize(self):
         self.check(self.lib.sphb200_ctx_synchronize(self.h))
 
+    def stage_wait(self):
+        self.check(self.lib.sphb200_ctx_stage_wait(self.h))
+
+    def fetch_wait(self):
+        self.check(self.lib.sphb200_ctx_fetch_wait(self.h))
+
     @property
     def stream(self):
         return self.lib.sphb200_ctx_stream(self.h)
@@ -223,6 +229,14 @@ class Body:
     def commit_staged(self):
         self.sys.check(self.lib.sphb200_body_commit_staged(self.h))
 
+    def fetch_async(self, name, host_ptr):
+        """asynchronous device -> host read (output / restart path); SPHSystem.fetch_wait() completes it"""
+        self.sys.check(self.lib.sphb200_var_fetch_async(self.h, name.encode(), C.c_void_p(host_ptr)))
+
+    def set_ids(self, original_id):
+        ids = np.ascontiguousarray(original_id, dtype=np.int64)
+        self.sys.check(self.lib.sphb200_ids_from_host(self.h, ids.ctypes.data_as(C.POINTER(C.c_int64))))
+
     def width(self, name):
         w = C.c_int()
         self.sys.check(self.lib.sphb200_var_width(self.h, name.encode(), C.byref(w)))
@@ -328,6 +342,13 @@ class Relation:
         counts = np.zeros(self.body.n, dtype=np.int32)
         self.sys.check(self.lib.sphb200_relation_neighbors(self.h, k, counts.ctypes.data_as(C.POINTER(C.c_int32)), None, C.byref(total)))
         return counts, int(total.value)
+
+    def stats(self, k=0):
+        out = (C.c_double * 8)()
+        self.sys.check(self.lib.sphb200_relation_stats(self.h, k, out))
+        o = list(out)
+        return {"pairs": int(o[0]), "masked_search": bool(o[1]), "index_list": bool(o[2]), "union_entries": int(o[3]),
+                "union_groups": int(o[4]), "group_size": int(o[5]), "n": int(o[6])}
 
     def neighbors(self, k=0):
         """(counts[n], flat j in list order) of target k - parity/debug"""
