@@ -159,8 +159,27 @@ sphb200_status sphb200_integration_1st_half(sphb200_relation *inner, sphb200_rel
 sphb200_status sphb200_integration_2nd_half(sphb200_relation *inner, sphb200_relation *wall_or_null, int riemann, double dt);
 /* ReduceDynamics<AcousticTimeStep> (fluid_dynamics/fluid_time_step.cpp:12-31): cfl*h/(max(c0+|v|)+tiny) */
 sphb200_status sphb200_acoustic_dt(sphb200_body *b, double cfl, double *dt_out);
-/* ReduceDynamics<AdvectionTimeStep|AdvectionViscousTimeStep> (fluid_time_step.cpp:44-79) */
+/* ReduceDynamics<AdvectionTimeStep|AdvectionViscousTimeStep> (fluid_time_step.cpp:44-79).  dt_out == NULL: the
+ * result stays on the device (the next sphb200_acoustic_relaxation with Dt < 0 uses it), no host synchronisation. */
 sphb200_status sphb200_advection_dt(sphb200_body *b, double U_ref, double cfl, int viscous, double *dt_out);
+/* The whole acoustic sub-step loop of one advection step,
+ *     while (relaxation_time < Dt) { Integration1stHalf; Integration2ndHalf; dt = AcousticTimeStep; ... }
+ * with dt, relaxation_time and the exit test resident on the device: every sub-step kernel reads dt from a control
+ * block and returns at once after the loop has ended, so the host queues sub-steps without waiting for the
+ * ReduceDynamics result (the reference's particle_reduce returns to the host every time,
+ * particle_iterators.h / src_sycl .../particle_iterators_sycl.h:80-105).  order selects the reference main's statement order:
+ *   0  dt = reduce; step(dt); relaxation_time += dt                  tests/2d_examples/test_2d_dambreak/Dambreak.cpp:183-192
+ *   1  step(dt of the previous sub-step); dt = reduce; relaxation_time += dt      tests/3d_examples/test_3d_dambreak/dambreak.cpp:168-177
+ *   2  dt = min(reduce, Dt); relaxation_time += dt; step(dt)         tests/2d_examples/test_2d_taylor_green/taylor_green.cpp:167-176
+ * Dt < 0: use the device-resident Dt of the last sphb200_advection_dt(..., NULL).  dt_carry >= 0 sets the dt the first
+ * sub-step integrates with (order 1), < 0 keeps the device's.  out5 != NULL: sub-steps are queued max_substeps at first,
+ * then 4 at a time until the device reports the end of the loop (one host synchronisation per batch) and
+ * out5 = {sub-steps done, last dt, accumulated physical time, relaxation_time, 1}.  out5 == NULL: exactly max_substeps
+ * launches are queued and the call returns without synchronising; sphb200_relaxation_state reads the block later
+ * (out5[4] = 0 there: the loop needs more sub-steps - call again with resume = 1). */
+sphb200_status sphb200_acoustic_relaxation(sphb200_relation *inner, sphb200_relation *wall_or_null, int riemann_1st, int riemann_2nd,
+                                           double Dt, double cfl, int order, double dt_carry, int max_substeps, int resume, double *out5);
+sphb200_status sphb200_relaxation_state(sphb200_ctx *ctx, double *out5);
 /* SimpleDynamics<GravityForce<Gravity>> (general_dynamics/force_prior.hpp:22-41) */
 sphb200_status sphb200_gravity_force(sphb200_body *b, const double *g);
 /* InteractionWithUpdate<ViscousForceInner> (fluid_dynamics/viscous_dynamics.hpp:35-53 + force_prior.hpp:22-26) */

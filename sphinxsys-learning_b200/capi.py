@@ -67,6 +67,8 @@ SIGNATURES = {
     "sphb200_integration_2nd_half": (_i, [_vp, _vp, _i, _d]),
     "sphb200_acoustic_dt": (_i, [_vp, _d, _dp]),
     "sphb200_advection_dt": (_i, [_vp, _d, _d, _i, _dp]),
+    "sphb200_acoustic_relaxation": (_i, [_vp, _vp, _i, _i, _d, _d, _i, _d, _i, _i, _dp]),
+    "sphb200_relaxation_state": (_i, [_vp, _dp]),
     "sphb200_gravity_force": (_i, [_vp, _dp]),
     "sphb200_viscous_force": (_i, [_vp]),
     "sphb200_transport_velocity_correction": (_i, [_vp, _d]),

@@ -86,7 +86,7 @@ def shell_normals(p, center, half_outer, half_inner):
 # ------------------------------------------------------------------------------------------------
 class DamBreak:
     def __init__(self, backend, ndim=3, dp=0.05, real_bytes=8, with_observer=True, fluid_box=None, tank=None, x_range=None,
-                 defer_configuration=False, **sys_kw):
+                 defer_configuration=False, fused_loop=True, **sys_kw):
         """x_range: keep only the lattice planes with x in [x_lo, x_hi) (one slab of a decomposed run);
         defer_configuration: stop before the first cell list / configuration (the slab driver finishes)"""
         dtype = np.float64 if real_bytes == 8 else np.float32
@@ -146,6 +146,8 @@ class DamBreak:
         self.n_advection = 0
         self.n_acoustic = 0
         self.dt = 0.0
+        self.fused_loop = fused_loop
+        self._substeps_guess = 6
         if defer_configuration:
             return
         # initializeSystemCellLinkedLists / Configurations; gravity prior force (dambreak.cpp:131-136)
@@ -181,6 +183,14 @@ class DamBreak:
         Dt = S.advection_dt(w, self.U_ref)
         S.density_summation(self.inner, self.wall_contact, free_surface=True)
         relaxation, k = 0.0, 0
+        if self.fused_loop and hasattr(S, "acoustic_relaxation"):
+            # the same loop, resident on the device (sphb200_acoustic_relaxation): no host round trip per sub-step
+            k, self.dt, _, relaxation = S.acoustic_relaxation(self.inner, self.wall_contact, True, True, Dt, 0.6,
+                                                              order=1 if self.ndim == 3 else 0, dt_carry=self.dt,
+                                                              max_substeps=self._substeps_guess)
+            self._substeps_guess = k + 1
+            self.time += relaxation
+            self.n_acoustic += k
         while relaxation < Dt:
             if self.ndim == 3:  # dambreak.cpp:168-177: step with the previous dt (0 at start), then reduce
                 self.acoustic_substep(self.dt)
@@ -211,8 +221,9 @@ class DamBreak:
 # 2-D Taylor-Green vortex
 # ------------------------------------------------------------------------------------------------
 class TaylorGreen:
-    def __init__(self, backend, dp=0.01, real_bytes=8, **sys_kw):
+    def __init__(self, backend, dp=0.01, real_bytes=8, fused_loop=True, **sys_kw):
         dtype = np.float64 if real_bytes == 8 else np.float32
+        self.fused_loop, self._substeps_guess = fused_loop, 6
         self.rho0, self.U_f, self.c0 = 1.0, 1.0, 10.0
         self.mu = self.rho0 * self.U_f * 1.0 / 100.0
         self.sys = backend.SPHSystem(2, [0.0, 0.0], [1.0, 1.0], dp, real_bytes=real_bytes, **sys_kw)
@@ -252,6 +263,11 @@ class TaylorGreen:
         S.viscous_force(self.inner)
         S.transport_velocity_correction(self.inner, 0.2)
         relaxation, k = 0.0, 0
+        if self.fused_loop and hasattr(S, "acoustic_relaxation"):
+            k, _, _, relaxation = S.acoustic_relaxation(self.inner, None, True, False, Dt, 0.6, order=2,
+                                                        max_substeps=self._substeps_guess)
+            self._substeps_guess = k + 1
+            self.time += relaxation
         while relaxation < Dt:
             dt = min(S.acoustic_dt(w), Dt)
             relaxation += dt

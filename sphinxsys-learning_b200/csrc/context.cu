@@ -57,9 +57,16 @@ sphb200_status getVar(sphb200_body *b, const char *name, int width, bool evolvin
 
 sphb200_status reduceReset(sphb200_ctx *ctx, int slot, bool for_min)
 {
-    unsigned long long init = for_min ? 0x7ff0000000000000ull /* +inf */ : 0ull;
-    SPHB_CUDA(ctx, cudaMemcpyAsync(static_cast<unsigned long long *>(ctx->reduce_dev.p) + slot, &init, 8,
-                                   cudaMemcpyHostToDevice, ctx->stream));
+    unsigned long long *dst = static_cast<unsigned long long *>(ctx->reduce_dev.p) + slot;
+    if (!for_min)
+    {
+        SPHB_CUDA(ctx, cudaMemsetAsync(dst, 0, 8, ctx->stream));
+        return SPHB200_OK;
+    }
+    // +inf comes from the last word of the pinned result line (a pageable source could make the copy synchronous)
+    unsigned long long *inf = static_cast<unsigned long long *>(ctx->reduce_host) + 63;
+    *inf = 0x7ff0000000000000ull;
+    SPHB_CUDA(ctx, cudaMemcpyAsync(dst, inf, 8, cudaMemcpyHostToDevice, ctx->stream));
     return SPHB200_OK;
 }
 sphb200_status reduceRead(sphb200_ctx *ctx, int slot, double *out)

@@ -53,7 +53,20 @@ struct FluidP
     // riemann_solver.h:55-92 constants for identical left/right fluids
     R inv_rho0c0_ave, rho0c0_geo_ave, inv_c0_ave, limiter_slope;
     int riemann;
+    const StepCtl *ctl; // device-resident dt / exit flag of the sub-step loop, or null: dt is the kernel argument
 };
+
+// dt of this launch: the kernel argument, or the device-resident one; false: the loop has ended, return at once
+template <class R>
+__device__ __forceinline__ bool stepDt(const StepCtl *ctl, R &dt)
+{
+    if (!ctl)
+        return true;
+    if (*reinterpret_cast<const volatile int *>(&ctl->done))
+        return false;
+    dt = R(*reinterpret_cast<const volatile double *>(&ctl->dt));
+    return true;
+}
 
 template <class R>
 static FluidP<R> makeFluidP(const sphb200_body *b, R h, bool riemann)
@@ -71,6 +84,7 @@ static FluidP<R> makeFluidP(const sphb200_body *b, R h, bool riemann)
     f.inv_c0_ave = R(0.5) * (f.rho0 + f.rho0) * f.inv_rho0c0_ave;
     f.limiter_slope = R(3.0);
     f.riemann = riemann ? 1 : 0;
+    f.ctl = b->ctx->ctl_active;
     return f;
 }
 
@@ -239,8 +253,13 @@ template <int D, class R>
 __global__ void __launch_bounds__(256)
     k_first_half_init(int64_t i0, int64_t n, R dt, R p0, R rho0, const typename Real4<R>::type *__restrict__ xV,
                       R *__restrict__ rho, const R *__restrict__ drho, R *__restrict__ p, R *__restrict__ pos,
-                      const R *__restrict__ vel, Rec8<R> *__restrict__ rec_a)
+                      const R *__restrict__ vel, Rec8<R> *__restrict__ rec_a, const StepCtl *__restrict__ ctl,
+                      unsigned long long *__restrict__ max_slot)
 {
+    if (!stepDt(ctl, dt))
+        return;
+    if (ctl && blockIdx.x == 0 && threadIdx.x == 0)
+        *max_slot = 0ull; // the interaction kernel of this sub-step maximises c0 + |v| into it (stream order: K1 before K2)
     int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (i < i0 || i >= n)
         return;
@@ -293,6 +312,8 @@ __global__ void __launch_bounds__(128, sizeof(R) == 8 ? SPHB_MINB_F64 : SPHB_MIN
                  const R *__restrict__ rho, const R *__restrict__ mass, const R *__restrict__ fprior, R *__restrict__ force,
                  R *__restrict__ drho, R *__restrict__ vel, unsigned long long *__restrict__ max_slot)
 {
+    if (!stepDt(fl.ctl, dt))
+        return;
     const GroupIdx gi = groupIndex(i0, n);
     const int lane = threadIdx.x & 31;
     const int64_t i = gi.ic;
@@ -424,6 +445,8 @@ __global__ void __launch_bounds__(128, sizeof(R) == 8 ? SPHB_MINB_F64 : SPHB_MIN
                   KernelP<R> kern_w, PeriodicP<D, R> per, FluidP<R> fl, R dt, R *__restrict__ pos, R *__restrict__ rho,
                   R *__restrict__ drho, R *__restrict__ force)
 {
+    if (!stepDt(fl.ctl, dt))
+        return;
     const GroupIdx gi = groupIndex(i0, n);
     const int lane = threadIdx.x & 31;
     const int64_t i = gi.ic;
@@ -1039,7 +1062,7 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
             SPHB_LAUNCH_CHECK(ctx);
         }
         k_first_half_init<D, R><<<gridFor(span, 256), 256, 0, ctx->stream>>>(b->own_begin, b->own_end, dt, fl.p0, fl.rho0, xV, rho, drho,
-                                                                           p, pos, vel, rec_a);
+                                                                           p, pos, vel, rec_a, fl.ctl, static_cast<unsigned long long *>(ctx->reduce_dev.p));
         SPHB_LAUNCH_CHECK(ctx);
     }
     if (stage & 2)
@@ -1050,7 +1073,8 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
         SPHB_TRY((makeContactP<D, R>(wall, tiled ? 4 | 16 : 4, wp, kern_w)));
         if (!tiled)
             SPHB_TRY(ensureList(inner, 0));
-        SPHB_TRY(reduceReset(ctx, 0, false));
+        if (!fl.ctl) // the device-resident loop resets the slot in K1, and only while the loop is live
+            SPHB_TRY(reduceReset(ctx, 0, false));
         auto *slot = static_cast<unsigned long long *>(ctx->reduce_dev.p);
         const int grid = groupGrid(b->own_begin, b->own_end, 128);
         if (tiled)
@@ -1068,7 +1092,7 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
                 SPHB_CUDA(ctx, b->wall_sum.ensure(size_t(b->n) * (D + 1) * sizeof(R)));
                 R *ws = static_cast<R *>(b->wall_sum.p);
                 k_first_half_wall<D, R, G><<<148 * 4, 128, 0, ctx->stream>>>(UW.base, b->own_begin, b->own_end, UW.queue, rec_a, uw.t[0],
-                                                                           makeTileKernelP<R>(kern_w), rho, mass, fprior, ws);
+                                                                           makeTileKernelP<R>(kern_w), rho, mass, fprior, ws, fl.ctl);
                 SPHB_LAUNCH_CHECK(ctx);
                 k_first_half_tile<D, R, G, true><<<gridFor(U.n_groups, 128), 128, 0, ctx->stream>>>(
                     U.base, b->own_begin, b->own_end, U.n_groups, rec_a, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern),
@@ -1149,7 +1173,7 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
             SPHB_CUDA(ctx, b->wall_sum.ensure(size_t(b->n) * (D + 1) * sizeof(R)));
             R *ws = static_cast<R *>(b->wall_sum.p);
             k_second_half_wall<D, R, G><<<148 * 4, 128, 0, ctx->stream>>>(UW.base, b->own_begin, b->own_end, UW.queue, rec_b, uw.t[0],
-                                                                        makeTileKernelP<R>(kern_w), R(fl.limiter_slope * fl.inv_c0_ave), ws);
+                                                                        makeTileKernelP<R>(kern_w), R(fl.limiter_slope * fl.inv_c0_ave), ws, fl.ctl);
             SPHB_LAUNCH_CHECK(ctx);
             k_second_half_tile<D, R, G, kWideLanes, true><<<gridFor(n_threads, 128), 128, 0, ctx->stream>>>(
                 U.base, b->own_begin, b->own_end, n_threads, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern), makeTileKernelP<R>(kern_w),
@@ -1168,6 +1192,60 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
                                                                               P.kern, kern_w, P.per, fl, R(dt_), pos, rho, drho, force);
     SPHB_LAUNCH_CHECK(ctx);
     return SPHB200_OK;
+}
+
+// ---- device-resident sub-step loop control (StepCtl, internal.cuh) ----
+static sphb200_status ensureStepCtl(sphb200_ctx *ctx)
+{
+    if (ctx->step_ctl.p)
+        return SPHB200_OK;
+    SPHB_CUDA(ctx, ctx->step_ctl.ensure(sizeof(StepCtl)));
+    SPHB_CUDA(ctx, cudaMemsetAsync(ctx->step_ctl.p, 0, sizeof(StepCtl), ctx->stream));
+    return SPHB200_OK;
+}
+__global__ void k_ctl_begin(StepCtl *ctl, double Dt, double dt_carry)
+{
+    if (Dt >= 0.0)
+        ctl->Dt = Dt; // else: left by sphb200_advection_dt(..., NULL)
+    if (dt_carry >= 0.0)
+        ctl->dt = dt_carry;
+    ctl->relax = 0.0;
+    ctl->count = 0;
+    ctl->done = 0;
+}
+// fluid_time_step.cpp:61-79 outputResult on the device (same expression, same rounding as the host variant)
+template <class R>
+__global__ void k_advection_ctl(StepCtl *ctl, const unsigned long long *slot, R cfl, R h, R speed_ref)
+{
+    const R m = R(__longlong_as_double((long long)*slot));
+    const R speed_max = sqrt_r(m);
+    ctl->Dt = double(cfl * h / (fmax(speed_max, speed_ref) + Tiny<R>::value));
+}
+// phase 0 (before the sub-step, orders 0 and 2): dt from the max slot.  phase 1 (after it): bookkeeping, order 1: new dt
+template <class R>
+__global__ void k_substep_ctl(StepCtl *ctl, const unsigned long long *slot, R cfl, R h, int order, int phase)
+{
+    if (ctl->done)
+        return;
+    const R m = R(__longlong_as_double((long long)*slot));
+    const double dt_new = double(cfl * h / (m + Tiny<R>::value)); // fluid_time_step.cpp:27-31
+    if (phase == 0)
+    {
+        double dt = dt_new;
+        if (order == 2)
+            dt = fmin(dt, ctl->Dt); // taylor_green.cpp:170 SMIN(get_fluid_time_step_size.exec(), Dt)
+        ctl->dt = dt;
+        return;
+    }
+    if (order == 1)
+        ctl->dt = dt_new;
+    const double dt = ctl->dt;
+    ctl->relax += dt;
+    ctl->time += dt;
+    ctl->count += 1;
+    ctl->count_total += 1;
+    if (!(ctl->relax < ctl->Dt))
+        ctl->done = 1;
 }
 
 template <int D, class R>
@@ -1215,15 +1293,86 @@ static sphb200_status advectionDt(sphb200_body *b, double U_ref, double cfl, int
                                                                static_cast<unsigned long long *>(ctx->reduce_dev.p) + 1);
         SPHB_LAUNCH_CHECK(ctx);
     }
-    double m;
-    SPHB_TRY(reduceRead(ctx, 1, &m));
     // fluid_time_step.cpp:61-79
     R speed_ref = R(U_ref);
     if (viscous)
         speed_ref = std::max(R(b->mu) / R(b->rho0) / P.h, speed_ref);
+    if (!dt_out)
+    { // device-resident: Dt goes to the sub-step loop's control block, the host is not involved
+        SPHB_TRY(ensureStepCtl(ctx));
+        k_advection_ctl<R><<<1, 1, 0, ctx->stream>>>(static_cast<StepCtl *>(ctx->step_ctl.p),
+                                                     static_cast<const unsigned long long *>(ctx->reduce_dev.p) + 1, R(cfl), P.h, speed_ref);
+        SPHB_LAUNCH_CHECK(ctx);
+        return SPHB200_OK;
+    }
+    double m;
+    SPHB_TRY(reduceRead(ctx, 1, &m));
     R speed_max = std::sqrt(R(m));
-    if (dt_out)
-        *dt_out = double(R(cfl) * P.h / (std::max(speed_max, speed_ref) + Tiny<R>::value));
+    *dt_out = double(R(cfl) * P.h / (std::max(speed_max, speed_ref) + Tiny<R>::value));
+    return SPHB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The acoustic sub-step loop of one advection step, device-resident (no host round trip per sub-step).
+// order 0: dt = AcousticTimeStep; step(dt); relax += dt            (2-D dam break, Dambreak.cpp:183-192)
+// order 1: step(dt carried from the previous sub-step); dt = AcousticTimeStep; relax += dt   (dambreak.cpp:168-177)
+// order 2: dt = min(AcousticTimeStep, Dt); relax += dt; step(dt)   (taylor_green.cpp:167-176)
+// ---------------------------------------------------------------------------------------------
+template <int D, class R>
+static sphb200_status acousticRelaxation(sphb200_relation *inner, sphb200_relation *wall, int riemann1, int riemann2, double Dt,
+                                         double cfl, int order, double dt_carry, int max_substeps, int resume, double *out4)
+{
+    sphb200_ctx *ctx = inner->ctx;
+    sphb200_body *b = inner->body;
+    BodyP<D, R> &P = b->P<D, R>();
+    SPHB_TRY(ensureStepCtl(ctx));
+    auto *ctl = static_cast<StepCtl *>(ctx->step_ctl.p);
+    auto *slot = static_cast<unsigned long long *>(ctx->reduce_dev.p);
+    if (order != 1)
+        SPHB_TRY((acousticDt<D, R>(b, cfl, nullptr))); // slot 0 = max(c0 + |v|) of the current velocities
+    if (!resume)
+    {
+        k_ctl_begin<<<1, 1, 0, ctx->stream>>>(ctl, Dt, dt_carry);
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    int launched = 0;
+    StepCtl host;
+    for (;;)
+    {
+        const int batch = out4 ? std::max(1, std::min(max_substeps - launched, launched == 0 ? max_substeps : 4)) : max_substeps;
+        ctx->ctl_active = ctl;
+        sphb200_status st = SPHB200_OK;
+        for (int k = 0; k < batch && st == SPHB200_OK; ++k)
+        {
+            if (order != 1)
+            {
+                k_substep_ctl<R><<<1, 1, 0, ctx->stream>>>(ctl, slot, R(cfl), P.h, order, 0);
+                ctx->launches++;
+            }
+            st = firstHalf<D, R>(inner, wall, riemann1, 0.0, 3);
+            if (st == SPHB200_OK)
+                st = secondHalf<D, R>(inner, wall, riemann2, 0.0);
+            k_substep_ctl<R><<<1, 1, 0, ctx->stream>>>(ctl, slot, R(cfl), P.h, order, 1);
+            ctx->launches++;
+        }
+        ctx->ctl_active = nullptr;
+        SPHB_TRY(st);
+        SPHB_CUDA(ctx, cudaGetLastError());
+        launched += batch;
+        if (!out4)
+            return SPHB200_OK;
+        SPHB_CUDA(ctx, cudaMemcpyAsync(ctx->reduce_host, ctl, sizeof(StepCtl), cudaMemcpyDeviceToHost, ctx->stream));
+        SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        memcpy(&host, ctx->reduce_host, sizeof(StepCtl));
+        if (host.done || launched >= 100000)
+            break;
+        max_substeps = launched + 4; // keep going in small batches until the device says the loop has ended
+    }
+    out4[0] = double(host.count);
+    out4[1] = host.dt;
+    out4[2] = host.time;
+    out4[3] = host.relax;
+    out4[4] = double(host.done);
     return SPHB200_OK;
 }
 
@@ -1394,6 +1543,34 @@ sphb200_status sphb200_acoustic_dt(sphb200_body *b, double cfl, double *dt_out)
         return SPHB200_ERR_INVALID;
     cudaSetDevice(b->ctx->device);
     return SPHB_DISPATCH(b->ctx, acousticDt, b, cfl, dt_out);
+}
+sphb200_status sphb200_acoustic_relaxation(sphb200_relation *inner, sphb200_relation *wall, int riemann_1st, int riemann_2nd, double Dt,
+                                           double cfl, int order, double dt_carry, int max_substeps, int resume, double *out5)
+{
+    if (!inner || order < 0 || order > 2 || max_substeps < 1)
+        return SPHB200_ERR_INVALID;
+    if (wall && wall->ctx != inner->ctx)
+        return inner->ctx->fail(SPHB200_ERR_INVALID, "acoustic_relaxation: relations from different contexts");
+    cudaSetDevice(inner->ctx->device);
+    return SPHB_DISPATCH(inner->ctx, acousticRelaxation, inner, wall, riemann_1st, riemann_2nd, Dt, cfl, order, dt_carry, max_substeps, resume, out5);
+}
+sphb200_status sphb200_relaxation_state(sphb200_ctx *ctx, double *out5)
+{
+    if (!ctx || !out5)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (!ctx->step_ctl.p)
+        return ctx->fail(SPHB200_ERR_INVALID, "relaxation_state: no acoustic_relaxation has run yet");
+    sphb::StepCtl host;
+    SPHB_CUDA(ctx, cudaMemcpyAsync(ctx->reduce_host, ctx->step_ctl.p, sizeof(sphb::StepCtl), cudaMemcpyDeviceToHost, ctx->stream));
+    SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    memcpy(&host, ctx->reduce_host, sizeof(host));
+    out5[0] = double(host.count);
+    out5[1] = host.dt;
+    out5[2] = host.time;
+    out5[3] = host.relax;
+    out5[4] = double(host.done);
+    return SPHB200_OK;
 }
 sphb200_status sphb200_advection_dt(sphb200_body *b, double U_ref, double cfl, int viscous, double *dt_out)
 {

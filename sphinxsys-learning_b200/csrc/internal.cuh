@@ -171,6 +171,21 @@ struct NeighborList
     bool expanded = false; // list holds this build's indices
 };
 
+// Device-resident control block of the acoustic sub-step loop (fluid.cu sphb200_acoustic_relaxation): the loop
+// `while (relaxation_time < Dt) { ... dt = AcousticTimeStep ... }` of the reference mains runs without the host -
+// every sub-step kernel reads dt (and the loop's exit flag) from here, k_substep_ctl advances it from the max slot.
+struct StepCtl
+{
+    double dt;     // acoustic time step the next sub-step integrates with
+    double relax;  // relaxation_time of the running advection step
+    double Dt;     // advection time step of the running advection step
+    double time;   // physical time accumulated over all sub-steps since ctx creation / reset
+    double dt_bound; // external upper bound folded into dt (slab runs: stays +inf here)
+    long long count_total;
+    int count;     // sub-steps done in the running advection step
+    int done;      // relax >= Dt: the remaining launches of this call return at once
+};
+
 // per-target device pointers handed to the interaction kernels
 template <class R>
 struct TargetP
@@ -231,6 +246,8 @@ struct sphb200_ctx
     std::vector<sphb200_body *> bodies;
     std::vector<sphb200_relation *> relations;
     sphb::DevBuf scratch_a, scratch_b, scan_tmp, reduce_dev, subkey_buf;
+    sphb::DevBuf step_ctl;                      // StepCtl, device side
+    const sphb::StepCtl *ctl_active = nullptr;  // non-null while sphb200_acoustic_relaxation queues its sub-steps
     void *reduce_host = nullptr; // pinned, 64 doubles
 
     sphb200_status fail(sphb200_status s, const std::string &msg)

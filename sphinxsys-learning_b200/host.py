@@ -133,6 +133,25 @@ class SPHSystem:
         self.check(self.lib.sphb200_advection_dt(body.h, U_ref, cfl, int(viscous), C.byref(out)))
         return out.value
 
+    def advection_dt_device(self, body, U_ref, cfl=0.25, viscous=False):
+        """Dt stays on the device (no host synchronisation); acoustic_relaxation(Dt=None) uses it"""
+        self.check(self.lib.sphb200_advection_dt(body.h, U_ref, cfl, int(viscous), None))
+
+    def acoustic_relaxation(self, inner, wall=None, riemann_1st=True, riemann_2nd=True, Dt=None, cfl=0.6, order=1, dt_carry=-1.0,
+                            max_substeps=8, wait=True, resume=False):
+        """the sub-step loop of one advection step on the device; wait=True returns (sub-steps, last dt, time, relaxation_time)"""
+        out = (C.c_double * 5)() if wait else None
+        self.check(self.lib.sphb200_acoustic_relaxation(inner.h, wall.h if wall else None, int(riemann_1st), int(riemann_2nd),
+                                                        -1.0 if Dt is None else Dt, cfl, int(order), dt_carry, int(max_substeps),
+                                                        int(resume), out))
+        if wait:
+            return int(out[0]), out[1], out[2], out[3]
+
+    def relaxation_state(self):
+        out = (C.c_double * 5)()
+        self.check(self.lib.sphb200_relaxation_state(self.h, out))
+        return {"substeps": int(out[0]), "dt": out[1], "time": out[2], "relaxation_time": out[3], "done": bool(out[4])}
+
     def gravity_force(self, body, g):
         g3 = (C.c_double * 3)(*list(g) + [0.0] * (3 - len(g)))
         self.check(self.lib.sphb200_gravity_force(body.h, g3))

@@ -553,6 +553,61 @@ def test_run_level_observables_against_the_reference_fixtures(pk, gpu):
     r = vg.taylor_green(51, backend=gpu)
     assert r["WaterBody_TotalKineticEnergy"]["dtw_ok"] and r["WaterBody_MaximumSpeed"]["dtw_ok"], r
     assert r["WaterBody_TotalKineticEnergy"]["first_sample_over_1pct"] >= 2, r@pytest.mark.gpu
+@pytest.mark.parametrize("which", ["dambreak_3d", "dambreak_2d", "taylor_green", "dambreak_3d_f32"])
+def test_device_resident_substep_loop_equals_the_host_driven_loop(pk, gpu, which):
+    """sphb200_acoustic_relaxation (dt, relaxation_time and the exit test on the device, no host round trip per
+    sub-step) against the same loop driven from the host with sphb200_acoustic_dt: identical (Dt, sub-steps)
+    sequence, identical dt and identical fields, bit for bit, in the three statement orders of the reference mains"""
+    def make(fused):
+        if which == "dambreak_3d":
+            return pk.cases.DamBreak(gpu, ndim=3, dp=0.05, real_bytes=8, fused_loop=fused)
+        if which == "dambreak_3d_f32":
+            return pk.cases.DamBreak(gpu, ndim=3, dp=0.05, real_bytes=4, fused_loop=fused)
+        if which == "dambreak_2d":
+            return pk.cases.DamBreak(gpu, ndim=2, dp=0.025, real_bytes=8, fused_loop=fused)
+        return pk.cases.TaylorGreen(gpu, dp=0.02, fused_loop=fused)
+    a, b = make(True), make(False)
+    seq_a = [a.advection_step() for _ in range(12)]
+    seq_b = [b.advection_step() for _ in range(12)]
+    assert seq_a == seq_b
+    assert a.n_acoustic == b.n_acoustic and a.n_acoustic > 12
+    assert abs(a.time - b.time) <= 1e-14 * b.time
+    if which != "taylor_green":
+        assert a.dt == b.dt
+    for nm in ("Position", "Velocity", "Density", "Pressure", "Force", "DensityChangeRate"):
+        assert np.array_equal(field(a.water, nm), field(b.water, nm)), nm
+    # the very next host-side AcousticTimeStep sees the same maximum
+    assert a.sys.acoustic_dt(a.water) == b.sys.acoustic_dt(b.water)
+
+
+@pytest.mark.gpu
+def test_substep_loop_without_any_host_synchronisation(pk, gpu):
+    """wait=False: Dt stays on the device (sphb200_advection_dt(..., NULL)), a fixed number of sub-steps is queued, the
+    surplus ones return at once; the state is read back once at the end and equals the host-driven run"""
+    a = pk.cases.DamBreak(gpu, ndim=3, dp=0.05, real_bytes=8)
+    b = pk.cases.DamBreak(gpu, ndim=3, dp=0.05, real_bytes=8, fused_loop=False)
+    S = a.sys
+    total = 0
+    for step in range(6):
+        S.advection_dt_device(a.water, a.U_ref)
+        S.density_summation(a.inner, a.wall_contact, free_surface=True)
+        S.acoustic_relaxation(a.inner, a.wall_contact, True, True, None, 0.6, order=1, dt_carry=0.0 if step == 0 else -1.0,
+                              max_substeps=3, wait=False)
+        st = S.relaxation_state()
+        while not st["done"]:                      # 3 was not enough: queue more, still the same advection step
+            S.acoustic_relaxation(a.inner, a.wall_contact, True, True, None, 0.6, order=1, max_substeps=2, wait=False, resume=True)
+            st = S.relaxation_state()
+        total += st["substeps"]
+        a.water.update_cell_list()
+        a.update_configuration()
+        Dt, k = b.advection_step(sort_interval=0)
+        assert st["substeps"] == k and st["dt"] == b.dt
+    assert abs(st["time"] - b.time) <= 1e-14 * b.time
+    for nm in ("Position", "Velocity", "Density"):
+        assert np.array_equal(field(a.water, nm), field(b.water, nm)), nm
+
+
+@pytest.mark.gpu
 def test_stage_then_resort_then_commit_is_a_reload(pk, gpu):
     """a cell_list_update between var_stage and body_commit_staged re-sorts the resident rows but not the
     staged ones.  The commit must then (a) refuse a partial set of evolving variables, (b) with the full set behave as
