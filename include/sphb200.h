@@ -182,8 +182,10 @@ sphb200_status sphb200_acoustic_relaxation(sphb200_relation *inner, sphb200_rela
 sphb200_status sphb200_relaxation_state(sphb200_ctx *ctx, double *out5);
 /* SimpleDynamics<GravityForce<Gravity>> (general_dynamics/force_prior.hpp:22-41) */
 sphb200_status sphb200_gravity_force(sphb200_body *b, const double *g);
-/* InteractionWithUpdate<ViscousForceInner> (fluid_dynamics/viscous_dynamics.hpp:35-53 + force_prior.hpp:22-26) */
-sphb200_status sphb200_viscous_force(sphb200_relation *inner);
+/* InteractionWithUpdate<ViscousForceInner> (fluid_dynamics/viscous_dynamics.hpp:35-53 + force_prior.hpp:22-26), or with
+ * wall_or_null != NULL InteractionWithUpdate<ViscousForceWithWall> = inner + ViscousForce<Contact<Wall>>
+ * (viscous_dynamics.hpp:92-115: 2 (v_i - v_wall) / (r + 0.01 h), weight 2 e.(B_i e) mu, added onto the inner force) */
+sphb200_status sphb200_viscous_force(sphb200_relation *inner, sphb200_relation *wall_or_null);
 /* InteractionWithUpdate<TransportVelocityCorrectionInner<…TruncatedLinear,AllParticles>>
  * (fluid_dynamics/transport_velocity_correction.hpp:38-67) */
 sphb200_status sphb200_transport_velocity_correction(sphb200_relation *inner, double coefficient);
@@ -191,6 +193,9 @@ sphb200_status sphb200_transport_velocity_correction(sphb200_relation *inner, do
 sphb200_status sphb200_total_kinetic_energy(sphb200_body *b, double *out);
 sphb200_status sphb200_total_mechanical_energy(sphb200_body *b, const double *g, double *out);
 sphb200_status sphb200_maximum_speed(sphb200_body *b, double *out);
+/* ReduceDynamics<PositionUpperBound | PositionLowerBound> (general_reduce.cpp:28-49): component-wise bound of the
+ * particle positions, out3[ndim..2] = 0.  The dam-break front position is the upper bound's x component. */
+sphb200_status sphb200_position_bound(sphb200_body *b, int upper, double *out3);
 /* ObservingAQuantity (general_dynamics/general_interpolation.h:63-83): out = n_observer*width doubles */
 sphb200_status sphb200_observe(sphb200_relation *contact, const char *name, int width, double *out);
 

@@ -489,7 +489,7 @@ class InteractionWithUpdate<fluid_dynamics::ViscousForceInner> : public BaseDyna
 {
   public:
     explicit InteractionWithUpdate(InnerRelation &inner) : inner_(inner) {}
-    void exec(Real = Real(0)) override { inner_.getSPHBody().ck(sphb200_viscous_force(inner_.handle()), "ViscousForce"); }
+    void exec(Real = Real(0)) override { inner_.getSPHBody().ck(sphb200_viscous_force(inner_.handle(), nullptr), "ViscousForce"); }
 
   private:
     InnerRelation &inner_;

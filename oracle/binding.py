@@ -41,10 +41,10 @@ def load():
         "orc_density_summation": (None, [vp, i, i, i]),
         "orc_integration_1st_half": (None, [vp, i, i, i, d]), "orc_integration_2nd_half": (None, [vp, i, i, i, d]),
         "orc_acoustic_dt": (d, [vp, i, d]), "orc_advection_dt": (d, [vp, i, d, d, i]),
-        "orc_gravity_force": (None, [vp, i, dp]), "orc_viscous_force": (None, [vp, i]),
+        "orc_gravity_force": (None, [vp, i, dp]), "orc_viscous_force": (None, [vp, i, i]),
         "orc_transport_velocity_correction": (None, [vp, i, d]),
         "orc_total_kinetic_energy": (d, [vp, i]), "orc_total_mechanical_energy": (d, [vp, i, dp]),
-        "orc_maximum_speed": (d, [vp, i]), "orc_observe": (None, [vp, i, cp, i, dp]),
+        "orc_maximum_speed": (d, [vp, i]), "orc_position_bound": (None, [vp, i, i, dp]), "orc_observe": (None, [vp, i, cp, i, dp]),
         "orc_correction_matrix": (None, [vp, i]), "orc_solid_1st_half": (None, [vp, i, i, d]),
         "orc_solid_2nd_half": (None, [vp, i, d]), "orc_solid_constrain": (None, [vp, i, lp, l]),
         "orc_solid_dt": (d, [vp, i, d]), "orc_num_threads": (i, []), "orc_set_num_threads": (i, [i]),
@@ -119,8 +119,8 @@ class SPHSystem:
     def gravity_force(self, body, g):
         self.lib.orc_gravity_force(self.h, body.id, self._g3(g))
 
-    def viscous_force(self, inner):
-        self.lib.orc_viscous_force(self.h, inner.id)
+    def viscous_force(self, inner, wall=None):
+        self.lib.orc_viscous_force(self.h, inner.id, wall.id if wall else -1)
 
     def transport_velocity_correction(self, inner, coefficient=0.2):
         self.lib.orc_transport_velocity_correction(self.h, inner.id, coefficient)
@@ -133,6 +133,11 @@ class SPHSystem:
 
     def maximum_speed(self, body):
         return self.lib.orc_maximum_speed(self.h, body.id)
+
+    def position_bound(self, body, upper=True):
+        out = (C.c_double * 3)()
+        self.lib.orc_position_bound(self.h, body.id, int(upper), out)
+        return np.asarray(list(out)[:self.ndim])
 
     def observe(self, contact, name, width=1):
         out = np.zeros(contact.body.n * width, dtype=np.float64)

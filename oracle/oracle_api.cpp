@@ -296,10 +296,17 @@ void orc_gravity_force(void *sys, int body, const double *g)
         gravityForce<D, R>(*S.bodies[body], gg);
     });
 }
-void orc_viscous_force(void *sys, int inner) { DISPATCH(sys, viscousForce<D, R>(*S.rels[inner])); }
+void orc_viscous_force(void *sys, int inner, int wall)
+{
+    DISPATCH(sys, viscousForce<D, R>(*S.rels[inner], wall >= 0 ? S.rels[wall].get() : nullptr));
+}
 void orc_transport_velocity_correction(void *sys, int inner, double coeff)
 {
     DISPATCH(sys, transportVelocityCorrection<D, R>(*S.rels[inner], R(coeff)));
+}
+void orc_position_bound(void *sys, int body, int upper, double *out3)
+{
+    DISPATCH(sys, positionBound<D, R>(*S.bodies[body], upper != 0, out3));
 }
 double orc_total_kinetic_energy(void *sys, int body)
 {

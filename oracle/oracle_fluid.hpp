@@ -281,9 +281,10 @@ void gravityForce(Body<D, R> &b, const R *g)
         }
 }
 
-// fluid_dynamics/viscous_dynamics.hpp:35-53 + force_prior.hpp:22-26 ; particle_functors.h:163-177
+// fluid_dynamics/viscous_dynamics.hpp:35-53 (inner), :92-115 (Contact<Wall>, added with +=) + force_prior.hpp:22-26 ;
+// particle_functors.h:163-177.  ComplexInteraction order: inner interaction, wall interaction, then update.
 template <int D, class R>
-void viscousForce(Relation<D, R> &inner)
+void viscousForce(Relation<D, R> &inner, Relation<D, R> *wall = nullptr)
 {
     Body<D, R> &b = *inner.body;
     R *Vol = b.v("VolumetricMeasure"), *vel = b.v("Velocity", D), *vf = b.v("ViscousForce", D),
@@ -313,6 +314,32 @@ void viscousForce(Relation<D, R> &inner)
         }
         for (int d = 0; d < D; ++d)
             vf[i * D + d] = f[d] * Vol[i];
+        if (wall)
+        {
+            R fw[D] = {};
+            for (size_t t = 0; t < wall->targets.size(); ++t)
+            {
+                R *wvel = wall->targets[t]->v("Velocity", D);
+                R *wVol = wall->targets[t]->v("VolumetricMeasure");
+                const auto &cn = wall->configs[t][i];
+                for (size_t k = 0; k != cn.current_size; ++k)
+                {
+                    size_t j = cn.j[k];
+                    const R *e = &cn.e[k * D];
+                    R ee = 0;
+                    for (int d = 0; d < D; ++d)
+                        ee += e[d] * (R(1.0) * e[d]);
+                    R denom = cn.r[k] + R(0.01) * h;
+                    for (int d = 0; d < D; ++d)
+                    {
+                        R vd = R(2.0) * (vel[i * D + d] - wvel[j * D + d]) / denom;
+                        fw[d] += R(2.0) * ee * mu_ij * vd * cn.dW[k] * wVol[j];
+                    }
+                }
+            }
+            for (int d = 0; d < D; ++d)
+                vf[i * D + d] += fw[d] * Vol[i];
+        }
     }
     for (long i = 0; i < n; ++i)
         for (int d = 0; d < D; ++d)
@@ -472,6 +499,22 @@ R maximumSpeed(Body<D, R> &b)
     for (size_t i = 0; i < b.n; ++i)
         m = std::max(m, vnorm<D, R>(vel + i * D));
     return m;
+}
+
+// general_dynamics/general_reduce.cpp:28-49 PositionLowerBound / PositionUpperBound (component-wise min / max)
+template <int D, class R>
+void positionBound(Body<D, R> &b, bool upper, double *out3)
+{
+    R *pos = b.v("Position", D);
+    for (int d = 0; d < 3; ++d)
+        out3[d] = 0.0;
+    for (int d = 0; d < D; ++d)
+    {
+        R m = upper ? std::numeric_limits<R>::lowest() : std::numeric_limits<R>::max();
+        for (size_t i = 0; i < b.n; ++i)
+            m = upper ? std::max(m, pos[i * D + d]) : std::min(m, pos[i * D + d]);
+        out3[d] = double(m);
+    }
 }
 
 // general_dynamics/general_interpolation.h:63-83 — observer interpolation of a width-wide variable

@@ -70,11 +70,12 @@ SIGNATURES = {
     "sphb200_acoustic_relaxation": (_i, [_vp, _vp, _i, _i, _d, _d, _i, _d, _i, _i, _dp]),
     "sphb200_relaxation_state": (_i, [_vp, _dp]),
     "sphb200_gravity_force": (_i, [_vp, _dp]),
-    "sphb200_viscous_force": (_i, [_vp]),
+    "sphb200_viscous_force": (_i, [_vp, _vp]),
     "sphb200_transport_velocity_correction": (_i, [_vp, _d]),
     "sphb200_total_kinetic_energy": (_i, [_vp, _dp]),
     "sphb200_total_mechanical_energy": (_i, [_vp, _dp, _dp]),
     "sphb200_maximum_speed": (_i, [_vp, _dp]),
+    "sphb200_position_bound": (_i, [_vp, _i, _dp]),
     "sphb200_observe": (_i, [_vp, _cp, _i, _dp]),
     "sphb200_correction_matrix": (_i, [_vp]),
     "sphb200_solid_1st_half": (_i, [_vp, _i, _d]),

@@ -689,8 +689,8 @@ __global__ void __launch_bounds__(256)
 
 template <int D, class R>
 __global__ void __launch_bounds__(128)
-    k_viscous(int64_t i0, int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, KernelP<R> kern,
-              PeriodicP<D, R> per, R mu, R h, const R *__restrict__ vel, R *__restrict__ vf, R *__restrict__ prev,
+    k_viscous(int64_t i0, int64_t n, const typename Real4<R>::type *__restrict__ xV, ListP<R> in, ContactP<R> wall, KernelP<R> kern,
+              KernelP<R> kern_w, PeriodicP<D, R> per, R mu, R h, const R *__restrict__ vel, R *__restrict__ vf, R *__restrict__ prev,
               R *__restrict__ fprior)
 {
     int64_t i = (i0 & ~int64_t(31)) + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
@@ -727,10 +727,39 @@ __global__ void __launch_bounds__(128)
         for (int a = 0; a < D; ++a)
             f[a] += c * (vi[a] - vj[a]);
     }
+    // ViscousForce<Contact<Wall>> (viscous_dynamics.hpp:92-115): 2 (v_i - v_wall) / (r + 0.01 h), 2 e.(B_i e) mu, added with += onto
+    // the inner force (two separate sums times Vol_i, as the reference forms them)
+    R fw[D];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        fw[a] = R(0);
+    for (int t = 0; t < wall.n; ++t)
+    {
+        const TargetP<R> &T = wall.t[t];
+        const u32 cw = T.count[i];
+        const u32 *lw = listBase(T.list, T.slice_off, i);
+        for (u32 k = 0; k < cw; ++k)
+        {
+            u32 j = listEntry(lw, k);
+            R xj[D], Vj, vw[D];
+            loadXj<D, R>(T.xV, j, xj, Vj);
+            loadVec<D, R>(T.vel, j, vw);
+            Pair<D, R> g;
+            pairGeometry<D, R>(xi, xj, kern_w, g);
+            R ee = R(0);
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+                ee += g.e[a] * g.e[a];
+            R c = R(2.0) * ee * mu_ij * g.dW * Vj / (g.r + R(0.01) * h);
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+                fw[a] += c * (R(2.0) * (vi[a] - vw[a]));
+        }
+    }
 #pragma unroll
     for (int a = 0; a < D; ++a)
     {
-        R v = f[a] * Vi;
+        R v = f[a] * Vi + fw[a] * Vi;
         vf[i * D + a] = v;
         fprior[i * D + a] += v - prev[i * D + a];
         prev[i * D + a] = v;
@@ -1398,6 +1427,68 @@ static sphb200_status observable(sphb200_body *b, int kind, const double *g, dou
     return SPHB200_OK;
 }
 
+// PositionUpperBound / PositionLowerBound (general_dynamics/general_reduce.cpp:28-49, ReduceUpperBound / ReduceLowerBound
+// reduce_functors.h): component-wise max / min of the particle positions - order-independent, hence exact.
+template <int D, class R>
+__global__ void __launch_bounds__(256) k_position_bound(int64_t i0, int64_t n, int upper, const R *__restrict__ pos, double *__restrict__ partial)
+{
+    __shared__ double sh[8][3];
+    double m[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+        m[a] = upper ? -INFINITY : INFINITY;
+    for (int64_t i = i0 + blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x)
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+        {
+            const double x = double(pos[i * D + a]);
+            m[a] = upper ? fmax(m[a], x) : fmin(m[a], x);
+        }
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+        m[a] = upper ? warpMax<double>(m[a]) : warpMin<double>(m[a]);
+    if ((threadIdx.x & 31) == 0)
+        for (int a = 0; a < 3; ++a)
+            sh[threadIdx.x >> 5][a] = m[a];
+    __syncthreads();
+    if (threadIdx.x < 3)
+    {
+        double t = sh[0][threadIdx.x];
+        for (int w = 1; w < 8; ++w)
+            t = upper ? fmax(t, sh[w][threadIdx.x]) : fmin(t, sh[w][threadIdx.x]);
+        partial[blockIdx.x * 3 + threadIdx.x] = t;
+    }
+}
+__global__ void k_position_bound_final(int nb, int upper, const double *__restrict__ partial, double *__restrict__ out)
+{
+    if (threadIdx.x < 3 && blockIdx.x == 0)
+    {
+        double t = partial[threadIdx.x];
+        for (int k = 1; k < nb; ++k)
+            t = upper ? fmax(t, partial[k * 3 + threadIdx.x]) : fmin(t, partial[k * 3 + threadIdx.x]);
+        out[threadIdx.x] = t;
+    }
+}
+template <int D, class R>
+static sphb200_status positionBound(sphb200_body *b, int upper, double *out3)
+{
+    sphb200_ctx *ctx = b->ctx;
+    R *pos;
+    SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos, true));
+    const int nb = 148 * 2;
+    SPHB_CUDA(ctx, ctx->scratch_a.ensure(size_t(nb + 1) * 3 * 8));
+    double *partial = static_cast<double *>(ctx->scratch_a.p);
+    k_position_bound<D, R><<<nb, 256, 0, ctx->stream>>>(b->own_begin, b->own_end, upper, pos, partial);
+    SPHB_LAUNCH_CHECK(ctx);
+    k_position_bound_final<<<1, 32, 0, ctx->stream>>>(nb, upper, partial, partial + nb * 3);
+    SPHB_LAUNCH_CHECK(ctx);
+    SPHB_CUDA(ctx, cudaMemcpyAsync(ctx->reduce_host, partial + nb * 3, 24, cudaMemcpyDeviceToHost, ctx->stream));
+    SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int a = 0; a < 3; ++a)
+        out3[a] = a < D ? static_cast<double *>(ctx->reduce_host)[a] : 0.0;
+    return SPHB200_OK;
+}
+
 template <int D, class R>
 static sphb200_status gravityForce(sphb200_body *b, const double *g)
 {
@@ -1416,11 +1507,13 @@ static sphb200_status gravityForce(sphb200_body *b, const double *g)
 }
 
 template <int D, class R>
-static sphb200_status viscousForce(sphb200_relation *inner)
+static sphb200_status viscousForce(sphb200_relation *inner, sphb200_relation *wall)
 {
     sphb200_ctx *ctx = inner->ctx;
     sphb200_body *b = inner->body;
     SPHB_TRY(checkRelation(inner, true, "viscous_force"));
+    if (wall)
+        SPHB_TRY(checkRelation(wall, false, "viscous_force"));
     if (b->own_end <= b->own_begin)
         return SPHB200_OK;
     BodyP<D, R> &P = b->P<D, R>();
@@ -1431,9 +1524,12 @@ static sphb200_status viscousForce(sphb200_relation *inner)
     SPHB_TRY(getVarPtr<R>(b, "PreviousViscousForce", D, &prev, true));
     SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
     SPHB_TRY(ensureList(inner, 0));
+    ContactP<R> wp;
+    KernelP<R> kern_w = P.kern;
+    SPHB_TRY((makeContactP<D, R>(wall, 2, wp, kern_w))); // wall velocity; per-particle index lists
     k_viscous<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
-        b->own_begin, b->own_end, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), P.kern, P.per,
-        R(b->mu), P.h, vel, vf, prev, fprior);
+        b->own_begin, b->own_end, static_cast<const typename Real4<R>::type *>(b->xV.p), listOf<R>(inner->lists[0]), wp, P.kern, kern_w,
+        P.per, R(b->mu), P.h, vel, vf, prev, fprior);
     SPHB_LAUNCH_CHECK(ctx);
     return SPHB200_OK;
 }
@@ -1579,6 +1675,13 @@ sphb200_status sphb200_advection_dt(sphb200_body *b, double U_ref, double cfl, i
     cudaSetDevice(b->ctx->device);
     return SPHB_DISPATCH(b->ctx, advectionDt, b, U_ref, cfl, viscous, dt_out);
 }
+sphb200_status sphb200_position_bound(sphb200_body *b, int upper, double *out3)
+{
+    if (!b || !out3)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, positionBound, b, upper, out3);
+}
 sphb200_status sphb200_gravity_force(sphb200_body *b, const double *g)
 {
     if (!b || !g)
@@ -1586,12 +1689,12 @@ sphb200_status sphb200_gravity_force(sphb200_body *b, const double *g)
     cudaSetDevice(b->ctx->device);
     return SPHB_DISPATCH(b->ctx, gravityForce, b, g);
 }
-sphb200_status sphb200_viscous_force(sphb200_relation *inner)
+sphb200_status sphb200_viscous_force(sphb200_relation *inner, sphb200_relation *wall)
 {
-    if (!inner)
+    if (!inner || (wall && wall->ctx != inner->ctx))
         return SPHB200_ERR_INVALID;
     cudaSetDevice(inner->ctx->device);
-    return SPHB_DISPATCH(inner->ctx, viscousForce, inner);
+    return SPHB_DISPATCH(inner->ctx, viscousForce, inner, wall);
 }
 sphb200_status sphb200_transport_velocity_correction(sphb200_relation *inner, double coefficient)
 {

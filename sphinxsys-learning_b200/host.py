@@ -156,8 +156,8 @@ class SPHSystem:
         g3 = (C.c_double * 3)(*list(g) + [0.0] * (3 - len(g)))
         self.check(self.lib.sphb200_gravity_force(body.h, g3))
 
-    def viscous_force(self, inner):
-        self.check(self.lib.sphb200_viscous_force(inner.h))
+    def viscous_force(self, inner, wall=None):
+        self.check(self.lib.sphb200_viscous_force(inner.h, wall.h if wall else None))
 
     def transport_velocity_correction(self, inner, coefficient=0.2):
         self.check(self.lib.sphb200_transport_velocity_correction(inner.h, coefficient))
@@ -177,6 +177,11 @@ class SPHSystem:
         out = C.c_double()
         self.check(self.lib.sphb200_maximum_speed(body.h, C.byref(out)))
         return out.value
+
+    def position_bound(self, body, upper=True):
+        out = (C.c_double * 3)()
+        self.check(self.lib.sphb200_position_bound(body.h, int(upper), out))
+        return np.asarray(list(out)[:self.ndim])
 
     def observe(self, contact, name, width=1):
         out = np.zeros(contact.body.n * width, dtype=np.float64)

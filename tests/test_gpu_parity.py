@@ -553,6 +553,100 @@ def test_run_level_observables_against_the_reference_fixtures(pk, gpu):
     r = vg.taylor_green(51, backend=gpu)
     assert r["WaterBody_TotalKineticEnergy"]["dtw_ok"] and r["WaterBody_MaximumSpeed"]["dtw_ok"], r
     assert r["WaterBody_TotalKineticEnergy"]["first_sample_over_1pct"] >= 2, r@pytest.mark.gpu
+@pytest.mark.parametrize("ndim,dp,real_bytes", [(3, 0.05, 8), (2, 0.025, 8), (3, 0.05, 4)])
+def test_viscous_force_with_wall(pk, gpu, oracle, ndim, dp, real_bytes):
+    """row a14: ViscousForceWithWall = ViscousForce<Inner<>> + ViscousForce<Contact<Wall>> (viscous_dynamics.hpp:35-53,92-115)
+    + ForcePrior::update, on the walled dam-break tank with a seeded velocity field and a moving wall"""
+    out = {}
+    for name, be in (("gpu", gpu), ("oracle", oracle)):
+        c = pk.cases.DamBreak(be, ndim=ndim, dp=dp, real_bytes=real_bytes)
+        c.water.set_fluid(c.rho0, c.c0, 0.05)
+        for nm, v in seeded_state(c).items():
+            set_field(c.water, nm, v)
+        rng = np.random.default_rng(11)
+        set_field(c.wall, "Velocity", rng.normal(0.0, 0.2, size=(c.wall.n, ndim)).astype(c.sys.dtype))
+        c.sys.viscous_force(c.inner, c.wall_contact)
+        first = {nm: field(c.water, nm) for nm in ("ViscousForce", "ForcePrior")}
+        set_field(c.water, "Velocity", 0.5 * field(c.water, "Velocity"))
+        c.sys.viscous_force(c.inner, c.wall_contact)      # second call: ForcePrior += new - previous
+        out[name] = (first, {nm: field(c.water, nm) for nm in ("ViscousForce", "ForcePrior", "PreviousViscousForce")})
+        inner_only = pk.cases.DamBreak(be, ndim=ndim, dp=dp, real_bytes=real_bytes)
+        inner_only.water.set_fluid(c.rho0, c.c0, 0.05)
+        for nm, v in seeded_state(inner_only).items():
+            set_field(inner_only.water, nm, v)
+        inner_only.sys.viscous_force(inner_only.inner)
+        near_wall = np.abs(first["ViscousForce"] - field(inner_only.water, "ViscousForce")).max(axis=1) > 0
+        assert 0 < near_wall.sum() < c.water.n         # the wall term is there, and only next to the wall
+    tol = FP_TOL[real_bytes]
+    for k in (0, 1):
+        for nm in out["gpu"][k]:
+            assert rel_l2(out["gpu"][k][nm], out["oracle"][k][nm]) < tol, (k, nm)
+
+
+@pytest.mark.gpu
+def test_front_position_and_body_bounds(pk, gpu, oracle):
+    """row g: the dam-break front position = PositionUpperBound[0] (general_reduce.cpp:40-49) and the lower bound, exact
+    (order-independent reductions) on a seeded state; then the front trajectory of a 3-D run against the oracle's (1 %)"""
+    for ndim, dp in ((3, 0.05), (2, 0.025)):
+        g, o = pk.cases.DamBreak(gpu, ndim=ndim, dp=dp), pk.cases.DamBreak(oracle, ndim=ndim, dp=dp)
+        for c in (g, o):
+            jitter(c.water, 0.3)
+        for upper in (True, False):
+            assert np.array_equal(g.sys.position_bound(g.water, upper), o.sys.position_bound(o.water, upper))
+    g, o = pk.cases.DamBreak(gpu, ndim=3, dp=0.05), pk.cases.DamBreak(oracle, ndim=3, dp=0.05)
+    front_g, front_o = [], []
+    while o.time < 1.2:
+        g.advection_step()
+        o.advection_step()
+        front_g.append(g.sys.position_bound(g.water)[0])
+        front_o.append(o.sys.position_bound(o.water)[0])
+    front_g, front_o = np.asarray(front_g), np.asarray(front_o)
+    assert front_o[-1] > 2.5                              # the front has left the initial column (x = 2)
+    assert np.abs(front_g - front_o).max() < 0.01 * front_o.max()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("real_bytes", [8, 4])
+def test_pairs_at_the_cutoff_through_the_tiled_kernels(pk, gpu, oracle, real_bytes):
+    """partners at rc (1 +- k ulp) go through the group-tiled density / 1st half / 2nd half, which
+    re-evaluate d.d < rc^2 with FMA contraction while the search rounded every product.  A pair the two decide
+    differently weighs (q - 2)^3 ~ 1e-45, so the sums must still match the oracle to the field tolerance"""
+    dp = 0.05
+    c_g = pk.cases.DamBreak(gpu, ndim=3, dp=dp, real_bytes=real_bytes)
+    c_o = pk.cases.DamBreak(oracle, ndim=3, dp=dp, real_bytes=real_bytes)
+    dtype = c_g.sys.dtype
+    rc = dtype(2) * (dtype(1.3) * dtype(dp))
+    rng = np.random.default_rng(5)
+    pos = field(c_g.water, "Position").astype(np.float64)
+    n = len(pos)
+    m = 600
+    src = rng.choice(n, size=m, replace=False)
+    dst = np.setdiff1d(np.arange(n), src)[:m]
+    u = rng.normal(size=(m, 3))
+    u /= np.linalg.norm(u, axis=1)[:, None]
+    ulp = np.finfo(dtype).eps
+    k = rng.integers(-3, 4, size=m)
+    moved = pos.copy()
+    moved[dst] = pos[src] + u * (float(rc) * (1.0 + k * ulp))[:, None]
+    inside = np.all((moved > 0.01) & (moved < np.array([1.99, 0.99, 0.49])), axis=1)
+    moved[~inside] = pos[~inside]
+    state = seeded_state(c_g)
+    for c in (c_g, c_o):
+        set_field(c.water, "Position", moved.astype(dtype))
+        for nm, v in state.items():
+            set_field(c.water, nm, v)
+        c.water.update_cell_list()
+        c.update_configuration()
+        c.sys.density_summation(c.inner, c.wall_contact, free_surface=True)
+        c.sys.integration_1st_half(c.inner, c.wall_contact, True, 1e-4)
+        c.sys.integration_2nd_half(c.inner, c.wall_contact, True, 1e-4)
+    assert c_g.inner.stats()["group_size"] == 2           # the tiled kernels ran
+    tol = FP_TOL[real_bytes]
+    for nm in ("Density", "Pressure", "Velocity", "Force", "DensityChangeRate", "Position"):
+        assert rel_l2(field(c_g.water, nm), field(c_o.water, nm)) < tol, nm
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("which", ["dambreak_3d", "dambreak_2d", "taylor_green", "dambreak_3d_f32"])
 def test_device_resident_substep_loop_equals_the_host_driven_loop(pk, gpu, which):
     """sphb200_acoustic_relaxation (dt, relaxation_time and the exit test on the device, no host round trip per
