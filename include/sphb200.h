@@ -180,6 +180,16 @@ sphb200_status sphb200_advection_dt(sphb200_body *b, double U_ref, double cfl, i
 sphb200_status sphb200_acoustic_relaxation(sphb200_relation *inner, sphb200_relation *wall_or_null, int riemann_1st, int riemann_2nd,
                                            double Dt, double cfl, int order, double dt_carry, int max_substeps, int resume, double *out5);
 sphb200_status sphb200_relaxation_state(sphb200_ctx *ctx, double *out5);
+/* The same loop in pieces, for a driver that interleaves its own work with the stages (the slab run: halo records
+ * between the stages, an all-reduce of the max slot over the ranks before the bookkeeping): relaxation_begin sets Dt
+ * and the carried dt; the stage entry points (integration_1st_half[_init|_interact], integration_2nd_half) called
+ * with dt < 0 read dt and the exit flag from the control block; substep_ctl(phase 0 | 1) is the before / after
+ * bookkeeping of one sub-step (see sphb200_acoustic_relaxation for `order`); reduce_slot_ptr gives the device address
+ * of reduction slot `slot` (0: bit pattern of max(c0 + |v|), a non-negative double - an integer MAX all-reduce of it
+ * over the ranks is exact). */
+sphb200_status sphb200_relaxation_begin(sphb200_ctx *ctx, double Dt, double dt_carry);
+sphb200_status sphb200_substep_ctl(sphb200_body *b, double cfl, int order, int phase);
+sphb200_status sphb200_reduce_slot_ptr(sphb200_ctx *ctx, int slot, void **out);
 /* SimpleDynamics<GravityForce<Gravity>> (general_dynamics/force_prior.hpp:22-41) */
 sphb200_status sphb200_gravity_force(sphb200_body *b, const double *g);
 /* InteractionWithUpdate<ViscousForceInner> (fluid_dynamics/viscous_dynamics.hpp:35-53 + force_prior.hpp:22-26), or with
@@ -246,6 +256,22 @@ sphb200_status sphb200_body_page_begin(sphb200_body *b, int page, int64_t *out);
  * which = 0: rec_a written by the 1st-half initialization, 1: rec_b written by the 1st-half update).  A
  * slab run overwrites the records of its halo copies with the owner's between the stages. */
 sphb200_status sphb200_body_record_ptr(sphb200_body *b, int which, void **out);
+/* Re-decomposition of a slab after an advection step, without a cell-list update of the old arrangement:
+ * slab_select classifies the rows by the axis-0 cell page of their CURRENT position (halo copies are dropped; owned
+ * rows stay if their page is still owned, go to the left slab if page <= page_lo, to the right one if page >=
+ * page_hi - 1 - as migrants or as that slab's fresh halo) and returns counts3 = {stay, to left, to right};
+ * slab_pack gathers the listed variables of the rows going to `side` (1 left, 2 right) into a row-major device
+ * buffer [count x sum(width)]; slab_rebuild makes the body {staying rows, rows received from the left, from the
+ * right} (every variable compacted in one pass, listed variables filled from the received buffers, the others
+ * zero), resets the ids and invalidates the cell list: ONE cell_list_update then sorts the new arrangement. */
+sphb200_status sphb200_slab_select(sphb200_body *b, int has_left, int has_right, int64_t *counts3);
+sphb200_status sphb200_slab_pack(sphb200_body *b, int side, const char *const *names, int n_names, void *out);
+sphb200_status sphb200_slab_rebuild(sphb200_body *b, const char *const *names, int n_names, const void *from_left, int64_t n_left,
+                                    const void *from_right, int64_t n_right);
+/* halo pack / unpack: dst[r] = src[idx[r]] and dst[idx[r]] = src[r] for n rows of row_bytes (multiple of 16) bytes,
+ * all device pointers, on the context's stream */
+sphb200_status sphb200_rows_gather(sphb200_ctx *ctx, const void *src, int row_bytes, const int64_t *idx, int64_t n, void *dst);
+sphb200_status sphb200_rows_scatter(sphb200_ctx *ctx, void *dst, int row_bytes, const int64_t *idx, int64_t n, const void *src);
 /* Dynamics1Level<Integration1stHalf...>::exec split into its two particle loops
  * (particle_dynamics/dynamics_algorithms.h:336-352): initialization (fluid_integration.hpp:50-55), then
  * interaction + update (:58-113), so that a slab run can refresh the halo pressures in between */

@@ -69,6 +69,14 @@ SIGNATURES = {
     "sphb200_advection_dt": (_i, [_vp, _d, _d, _i, _dp]),
     "sphb200_acoustic_relaxation": (_i, [_vp, _vp, _i, _i, _d, _d, _i, _d, _i, _i, _dp]),
     "sphb200_relaxation_state": (_i, [_vp, _dp]),
+    "sphb200_relaxation_begin": (_i, [_vp, _d, _d]),
+    "sphb200_substep_ctl": (_i, [_vp, _d, _i, _i]),
+    "sphb200_reduce_slot_ptr": (_i, [_vp, _i, _vpp]),
+    "sphb200_slab_select": (_i, [_vp, _i, _i, _i64p]),
+    "sphb200_slab_pack": (_i, [_vp, _i, C.POINTER(C.c_char_p), _i, _vp]),
+    "sphb200_slab_rebuild": (_i, [_vp, C.POINTER(C.c_char_p), _i, _vp, _i64, _vp, _i64]),
+    "sphb200_rows_gather": (_i, [_vp, _vp, _i, _vp, _i64, _vp]),
+    "sphb200_rows_scatter": (_i, [_vp, _vp, _i, _vp, _i64, _vp]),
     "sphb200_gravity_force": (_i, [_vp, _dp]),
     "sphb200_viscous_force": (_i, [_vp, _vp]),
     "sphb200_transport_velocity_correction": (_i, [_vp, _d]),

@@ -56,6 +56,8 @@ struct FluidP
     const StepCtl *ctl; // device-resident dt / exit flag of the sub-step loop, or null: dt is the kernel argument
 };
 
+static sphb200_status ensureStepCtl(sphb200_ctx *ctx);
+
 // dt of this launch: the kernel argument, or the device-resident one; false: the loop has ended, return at once
 template <class R>
 __device__ __forceinline__ bool stepDt(const StepCtl *ctl, R &dt)
@@ -1065,6 +1067,11 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
     SPHB_TRY((ensurePacked<D, R>(b)));
     SPHB_TRY((ensureRecBuffers<D, R>(b)));
     FluidP<R> fl = makeFluidP<R>(b, P.h, riemann != 0);
+    if (dt_ < 0.0 && !fl.ctl)
+    { // dt < 0 = the device-resident dt of the sub-step loop's control block (split stages of a slab run)
+        SPHB_TRY(ensureStepCtl(ctx));
+        fl.ctl = static_cast<const StepCtl *>(ctx->step_ctl.p);
+    }
     R *rho, *p, *drho, *mass, *pos, *vel, *force, *fprior;
     SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
     SPHB_TRY(getVarPtr<R>(b, "Pressure", 1, &p, true));
@@ -1169,6 +1176,11 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
     if (!tiled)
         SPHB_TRY(ensureList(inner, 0));
     FluidP<R> fl = makeFluidP<R>(b, P.h, riemann != 0);
+    if (dt_ < 0.0 && !fl.ctl)
+    {
+        SPHB_TRY(ensureStepCtl(ctx));
+        fl.ctl = static_cast<const StepCtl *>(ctx->step_ctl.p);
+    }
     R *rho, *drho, *pos, *vel, *force, *p;
     SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
     SPHB_TRY(getVarPtr<R>(b, "DensityChangeRate", 1, &drho, true));
@@ -1649,6 +1661,41 @@ sphb200_status sphb200_acoustic_relaxation(sphb200_relation *inner, sphb200_rela
         return inner->ctx->fail(SPHB200_ERR_INVALID, "acoustic_relaxation: relations from different contexts");
     cudaSetDevice(inner->ctx->device);
     return SPHB_DISPATCH(inner->ctx, acousticRelaxation, inner, wall, riemann_1st, riemann_2nd, Dt, cfl, order, dt_carry, max_substeps, resume, out5);
+}
+// the pieces of sphb200_acoustic_relaxation for a driver that interleaves its own work (halo exchange, all-reduce of the
+// max slot over the ranks) with the stages: begin -> per sub-step { stages with dt < 0 ..., substep_ctl } -> relaxation_state
+sphb200_status sphb200_relaxation_begin(sphb200_ctx *ctx, double Dt, double dt_carry)
+{
+    if (!ctx)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    SPHB_TRY(ensureStepCtl(ctx));
+    k_ctl_begin<<<1, 1, 0, ctx->stream>>>(static_cast<sphb::StepCtl *>(ctx->step_ctl.p), Dt, dt_carry);
+    SPHB_LAUNCH_CHECK(ctx);
+    return SPHB200_OK;
+}
+sphb200_status sphb200_substep_ctl(sphb200_body *b, double cfl, int order, int phase)
+{
+    if (!b || order < 0 || order > 2 || phase < 0 || phase > 1)
+        return SPHB200_ERR_INVALID;
+    sphb200_ctx *ctx = b->ctx;
+    cudaSetDevice(ctx->device);
+    SPHB_TRY(ensureStepCtl(ctx));
+    auto *ctl = static_cast<sphb::StepCtl *>(ctx->step_ctl.p);
+    auto *slot = static_cast<const unsigned long long *>(ctx->reduce_dev.p);
+    if (ctx->real_bytes == 8)
+        k_substep_ctl<double><<<1, 1, 0, ctx->stream>>>(ctl, slot, cfl, b->h_ratio * b->dp, order, phase);
+    else
+        k_substep_ctl<float><<<1, 1, 0, ctx->stream>>>(ctl, slot, float(cfl), float(b->h_ratio) * float(b->dp), order, phase);
+    SPHB_LAUNCH_CHECK(ctx);
+    return SPHB200_OK;
+}
+sphb200_status sphb200_reduce_slot_ptr(sphb200_ctx *ctx, int slot, void **out)
+{
+    if (!ctx || !out || slot < 0 || slot > 7)
+        return SPHB200_ERR_INVALID;
+    *out = static_cast<unsigned long long *>(ctx->reduce_dev.p) + slot;
+    return SPHB200_OK;
 }
 sphb200_status sphb200_relaxation_state(sphb200_ctx *ctx, double *out5)
 {

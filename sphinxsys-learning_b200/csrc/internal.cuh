@@ -289,6 +289,9 @@ struct sphb200_body
     // the rest are halo copies that only serve as neighbours j.  Defaults to the whole body.
     int64_t own_begin = 0, own_end = 0;
     int page_lo = -1, page_hi = -1; // owned range of cell pages along axis 0 (x slowest), or -1
+    sphb::DevBuf slab_flags, slab_idx[3]; // slab.cu slab_select: rows that stay / go to the left / to the right slab
+    int64_t slab_count[3] = {0, 0, 0};
+    bool slab_selected = false;
 
     template <int D, class R>
     sphb::BodyP<D, R> &P() { return *reinterpret_cast<sphb::BodyP<D, R> *>(params); }

@@ -147,6 +147,23 @@ class SPHSystem:
         if wait:
             return int(out[0]), out[1], out[2], out[3]
 
+    def relaxation_begin(self, Dt, dt_carry=-1.0):
+        self.check(self.lib.sphb200_relaxation_begin(self.h, Dt, dt_carry))
+
+    def substep_ctl(self, body, cfl=0.6, order=1, phase=1):
+        self.check(self.lib.sphb200_substep_ctl(body.h, cfl, int(order), int(phase)))
+
+    def reduce_slot_ptr(self, slot=0):
+        p = C.c_void_p()
+        self.check(self.lib.sphb200_reduce_slot_ptr(self.h, int(slot), C.byref(p)))
+        return p.value
+
+    def rows_gather(self, src_ptr, row_bytes, idx_ptr, n, dst_ptr):
+        self.check(self.lib.sphb200_rows_gather(self.h, C.c_void_p(src_ptr), int(row_bytes), C.c_void_p(idx_ptr), int(n), C.c_void_p(dst_ptr)))
+
+    def rows_scatter(self, dst_ptr, row_bytes, idx_ptr, n, src_ptr):
+        self.check(self.lib.sphb200_rows_scatter(self.h, C.c_void_p(dst_ptr), int(row_bytes), C.c_void_p(idx_ptr), int(n), C.c_void_p(src_ptr)))
+
     def relaxation_state(self):
         out = (C.c_double * 5)()
         self.check(self.lib.sphb200_relaxation_state(self.h, out))
@@ -324,6 +341,21 @@ class Body:
         b, e = C.c_int64(), C.c_int64()
         self.sys.check(self.lib.sphb200_body_owned_range(self.h, C.byref(b), C.byref(e)))
         return b.value, e.value
+
+    def slab_select(self, has_left, has_right):
+        """(stay, to left, to right) row counts of the re-decomposition (sphb200_slab_select)"""
+        out = (C.c_int64 * 3)()
+        self.sys.check(self.lib.sphb200_slab_select(self.h, int(has_left), int(has_right), out))
+        return int(out[0]), int(out[1]), int(out[2])
+
+    def slab_pack(self, side, names, out_ptr):
+        arr = (C.c_char_p * len(names))(*[n.encode() for n in names])
+        self.sys.check(self.lib.sphb200_slab_pack(self.h, int(side), arr, len(names), C.c_void_p(out_ptr)))
+
+    def slab_rebuild(self, names, left_ptr, n_left, right_ptr, n_right):
+        arr = (C.c_char_p * len(names))(*[n.encode() for n in names])
+        self.sys.check(self.lib.sphb200_slab_rebuild(self.h, arr, len(names), C.c_void_p(left_ptr), int(n_left), C.c_void_p(right_ptr), int(n_right)))
+        self.n = self.info()["n"]
 
     def keep_range(self, begin, end):
         self.sys.check(self.lib.sphb200_body_keep_range(self.h, int(begin), int(end)))

@@ -10,8 +10,11 @@ interaction+update -> halo records rec_b (new v) -> 2nd half -> min all-reduce o
 Per advection step:     one exchange that carries migrating particles AND the fresh halo (each rank
 sends its particles lying in the two pages either side of a cut), then sort + relations + halo index maps.
 
-The ranks' kernels are libsphb200's (host.py); torch is the plumbing only: views of device memory,
-index_select/index_copy_ for the halo pack/unpack, torch.distributed (NCCL) send/recv and all-reduce.
+The ranks' kernels are libsphb200's (host.py), including the halo pack/unpack (sphb200_rows_gather/scatter), the
+re-decomposition (sphb200_slab_select/pack/rebuild: one cell-list update per advection step) and the sub-step loop's
+bookkeeping (dt, relaxation time and the exit test stay on the device; the ranks all-reduce the bit pattern of
+max(c0+|v|) on the device, the host is not in the sub-step loop).  torch is the plumbing only: views of device
+memory, buffers, torch.distributed (NCCL) send/recv and all-reduce.
 `LocalComm` runs all slabs inside one process on one GPU (tests, single-GPU boxes); `DistComm` is one
 slab per process.
 """
@@ -92,6 +95,13 @@ class LocalComm:
         v = min(values) if op == "min" else (max(values) if op == "max" else sum(values))
         return v
 
+    def allreduce_max_device(self, slots):
+        """slots: one int64 device tensor per local slab (bit pattern of a non-negative double): all get the maximum"""
+        if len(slots) > 1:
+            m = torch.stack(slots).max(dim=0).values
+            for t in slots:
+                t.copy_(m)
+
     def barrier(self):
         pass
 
@@ -160,6 +170,9 @@ class DistComm:
         dist.all_reduce(t, op={"min": dist.ReduceOp.MIN, "max": dist.ReduceOp.MAX, "sum": dist.ReduceOp.SUM}[op])
         return float(t.item())
 
+    def allreduce_max_device(self, slots):
+        dist.all_reduce(slots[0], op=dist.ReduceOp.MAX)  # stays on the device: no host synchronisation
+
     def barrier(self):
         dist.barrier()
 
@@ -185,9 +198,13 @@ class _Part:
 class SlabDamBreak:
     """tests/3d_examples/test_3d_dambreak/dambreak.cpp:159-195 over n_slabs slabs; same loop as cases.DamBreak"""
 
-    def __init__(self, backend, comm, dp=0.05, real_bytes=8, device=0, stream=None, ndim=3):
+    def __init__(self, backend, comm, dp=0.05, real_bytes=8, device=0, stream=None, ndim=3, device_loop=True, fast_reconfigure=True):
+        """device_loop: dt / relaxation time / exit test of the sub-step loop on the device (False: one host round trip
+        per sub-step, the round-1 path); fast_reconfigure: sphb200_slab_select/pack/rebuild and one cell-list update
+        per advection step (False: keep_range + two cell-list updates + torch.cat, the round-1 path)"""
         assert torch is not None
         self.comm, self.dp, self.ndim, self.real_bytes = comm, dp, ndim, real_bytes
+        self.device_loop, self.fast_reconfigure, self._guess = device_loop, fast_reconfigure, 5
         self.device = torch.device("cuda", device)
         self.np_real = np.float64 if real_bytes == 8 else np.float32
         self.np_int = np.int64 if real_bytes == 8 else np.int32
@@ -266,20 +283,31 @@ class SlabDamBreak:
             P.recv_left = torch.argsort(gid[0:ob], stable=True) if P.has_left else None
             P.recv_right = (oe + torch.argsort(gid[oe:w.n], stable=True)) if P.has_right else None
             P.rec = [dev_tensor(w.record_ptr(k), (w.n, 8), self.np_real, self.device) for k in (0, 1)]
+            P.rec_ptr = [w.record_ptr(k) for k in (0, 1)]
+            t_real = P.rec[0].dtype
+            P.send_buf = [torch.empty((ix.numel() if ix is not None else 0, 8), dtype=t_real, device=self.device)
+                          for ix in (P.send_left, P.send_right)]
+            P.recv_buf = [torch.empty((ix.numel() if ix is not None else 0, 8), dtype=t_real, device=self.device)
+                          for ix in (P.recv_left, P.recv_right)]
+            P.slot = dev_tensor(P.case.sys.reduce_slot_ptr(0), (1,), np.int64, self.device)
 
     def _halo_records(self, which):
+        """owner's records of the rows in the neighbour's halo: pack (sphb200_rows_gather) -> send/recv -> unpack (rows_scatter)"""
         sends, rows = [], []
+        row_bytes = 8 * self.real_bytes
         for P in self.parts:
-            rec = P.rec[which]
-            sends.append((rec.index_select(0, P.send_left) if P.has_left else None,
-                          rec.index_select(0, P.send_right) if P.has_right else None))
+            S = P.case.sys
+            for side, ix in ((0, P.send_left), (1, P.send_right)):
+                if ix is not None and ix.numel():
+                    S.rows_gather(P.rec_ptr[which], row_bytes, ix.data_ptr(), ix.numel(), P.send_buf[side].data_ptr())
+            sends.append((P.send_buf[0] if P.has_left else None, P.send_buf[1] if P.has_right else None))
             rows.append((P.recv_left.numel() if P.has_left else 0, P.recv_right.numel() if P.has_right else 0))
         recvs = _exchange_fixed(self.comm, sends, rows)
         for P, (fl, fr) in zip(self.parts, recvs):
-            if P.has_left:
-                P.rec[which].index_copy_(0, P.recv_left, fl)
-            if P.has_right:
-                P.rec[which].index_copy_(0, P.recv_right, fr)
+            S = P.case.sys
+            for ix, t in ((P.recv_left, fl), (P.recv_right, fr)):
+                if ix is not None and ix.numel():
+                    S.rows_scatter(P.rec_ptr[which], row_bytes, ix.data_ptr(), ix.numel(), t.data_ptr())
 
     # ---- the loop ---------------------------------------------------------------------------------
     def _min_over_slabs(self, fn):
@@ -299,11 +327,42 @@ class SlabDamBreak:
             P.case.sys.integration_2nd_half(P.case.inner, P.case.wall_contact, True, dt)
         self.n_acoustic += 1
 
+    def _substep_device(self):
+        """one sub-step with dt < 0 = the device-resident dt; the ranks' maxima of c0+|v| are all-reduced on the device"""
+        for P in self.parts:
+            if P.oe <= P.ob:
+                P.slot.zero_()
+            P.case.sys.integration_1st_half_init(P.case.inner, -1.0)
+        self._halo_records(0)
+        for P in self.parts:
+            P.case.sys.integration_1st_half_interact(P.case.inner, P.case.wall_contact, True, -1.0)
+        self._halo_records(1)
+        for P in self.parts:
+            P.case.sys.integration_2nd_half(P.case.inner, P.case.wall_contact, True, -1.0)
+        self.comm.allreduce_max_device([P.slot for P in self.parts])
+        for P in self.parts:
+            P.case.sys.substep_ctl(P.case.water, 0.6, 1, 1)
+
     def advection_step(self):
         Dt = self._min_over_slabs(lambda P: P.case.sys.advection_dt(P.case.water, self.U_ref))
         for P in self.parts:
             P.case.sys.density_summation(P.case.inner, P.case.wall_contact, free_surface=True)
         relaxation, k = 0.0, 0
+        if self.device_loop:
+            for P in self.parts:
+                P.case.sys.relaxation_begin(Dt, self.dt)
+            batch = self._guess
+            while True:
+                for _ in range(batch):
+                    self._substep_device()
+                st = self.parts[0].case.sys.relaxation_state()   # the one host synchronisation of the loop
+                if st["done"]:
+                    break
+                batch = 1
+            k, self.dt, relaxation = st["substeps"], st["dt"], st["relaxation_time"]
+            self._guess = k
+            self.time += relaxation
+            self.n_acoustic += k
         while relaxation < Dt:  # dambreak.cpp:168-177: step with the previous dt, then reduce
             self.acoustic_substep(self.dt)
             self.dt = self._min_over_slabs(lambda P: P.case.sys.acoustic_dt(P.case.water))
@@ -315,7 +374,34 @@ class SlabDamBreak:
         return Dt, k
 
     def reconfigure(self):
-        """migration + fresh halo in one exchange, then sort, relations and halo maps"""
+        """migration + fresh halo in one exchange, then ONE sort, relations and halo maps"""
+        if not self.fast_reconfigure:
+            return self.reconfigure_two_sorts()
+        sends = []
+        for P in self.parts:
+            w = P.case.water
+            _, n_l, n_r = w.slab_select(P.has_left, P.has_right)
+            width = sum(w.width(nm) for nm in MIGRATE_VARS)
+            t_real = torch.float64 if self.real_bytes == 8 else torch.float32
+            bl = torch.empty((n_l, width), dtype=t_real, device=self.device)
+            br = torch.empty((n_r, width), dtype=t_real, device=self.device)
+            if n_l:
+                w.slab_pack(1, MIGRATE_VARS, bl.data_ptr())
+            if n_r:
+                w.slab_pack(2, MIGRATE_VARS, br.data_ptr())
+            sends.append((bl if P.has_left else None, br if P.has_right else None))
+        recvs = self.comm.exchange(sends)
+        for P, (fl, fr) in zip(self.parts, recvs):
+            w = P.case.water
+            nl = fl.shape[0] if fl is not None else 0
+            nr = fr.shape[0] if fr is not None else 0
+            w.slab_rebuild(MIGRATE_VARS, fl.data_ptr() if nl else 0, nl, fr.data_ptr() if nr else 0, nr)
+            w.update_cell_list()
+            P.case.update_configuration(observer=False)
+        self._halo_maps()
+
+    def reconfigure_two_sorts(self):
+        """the round-1 path (kept for A/B timing and as a cross-check of the fast one)"""
         sends = []
         for P in self.parts:
             w = P.case.water

@@ -83,12 +83,15 @@ def test_dist_comm_protocol_over_gloo(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n_slabs,real_bytes,pair_kernel", [(2, 8, -1), (3, 8, 0), (2, 4, -1), (3, 4, 1)])
-def test_slabs_equal_single_gpu(pk, gpu, slab, n_slabs, real_bytes, pair_kernel):
-    """N slabs emulated in one process (LocalComm) against the undecomposed run"""
-    dp, steps = 0.05, 6
+@pytest.mark.parametrize("n_slabs,real_bytes,pair_kernel,round1_path",
+                         [(2, 8, -1, False), (3, 8, 0, False), (2, 4, -1, False), (3, 4, 1, False), (4, 8, -1, False), (3, 8, -1, True)])
+def test_slabs_equal_single_gpu(pk, gpu, slab, n_slabs, real_bytes, pair_kernel, round1_path):
+    """N slabs emulated in one process (LocalComm) against the undecomposed run; round1_path: host-driven sub-step
+    loop and the two-sort reconfigure instead of the device-resident loop and sphb200_slab_select/pack/rebuild"""
+    dp, steps = 0.05, 8
     one = pk.cases.DamBreak(gpu, ndim=3, dp=dp, real_bytes=real_bytes, with_observer=False)
-    many = slab.SlabDamBreak(gpu, slab.LocalComm(n_slabs), dp=dp, real_bytes=real_bytes)
+    many = slab.SlabDamBreak(gpu, slab.LocalComm(n_slabs), dp=dp, real_bytes=real_bytes, device_loop=not round1_path,
+                             fast_reconfigure=not round1_path)
     one.sys.set_pair_kernel(pair_kernel)
     for P in many.parts:
         P.case.sys.set_pair_kernel(pair_kernel)
