@@ -44,6 +44,25 @@ def test_cpp_adapter_main_builds_and_fails_loudly_without_a_gpu(pk):
     assert r.returncode == 1 and "no CUDA device" in r.stderr
 
 
+def test_reference_main_compiles_unmodified_on_the_cuda_policy():
+    """integration/: the reference's tests/3d_examples/test_3d_dambreak/dambreak.cpp, read where it lies and not a byte
+    changed, compiles against the class skeleton + the CUDA execution policy (src_cuda) + libsphb200; without a GPU the
+    binary fails loudly (the reference's convention: message + exit 1)"""
+    import subprocess
+    import torch
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "integration")])
+    exe = os.path.join(ROOT, "integration", "_build", "test_3d_dambreak_cuda")
+    if not os.path.exists("/root/reference") and not os.path.exists(exe):
+        pytest.skip("reference tree absent and no prebuilt binary")
+    assert os.path.exists(exe)
+    mk = open(os.path.join(ROOT, "integration", "Makefile")).read()
+    assert "$(REF)/tests/3d_examples/test_3d_dambreak/dambreak.cpp" in mk  # compiled from the reference tree, not from a copy
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present: the run itself is covered by the gpu tests")
+    r = subprocess.run([exe, "--state_recording=0"], capture_output=True, text=True)
+    assert r.returncode == 1 and "no CUDA device" in r.stdout + r.stderr
+
+
 def test_product_package_never_touches_the_oracle():
     pkg = os.path.join(ROOT, "sphinxsys-learning_b200")
     for dirpath, _, files in os.walk(pkg):
