@@ -855,6 +855,12 @@ __global__ void __launch_bounds__(128)
 }
 
 } // namespace sphb
+#ifndef SPHB_QUAD_DEFAULT_F64
+#define SPHB_QUAD_DEFAULT_F64 2
+#endif
+#ifndef SPHB_QUAD_DEFAULT_F32
+#define SPHB_QUAD_DEFAULT_F32 0
+#endif
 #include "tile.cuh"
 namespace sphb
 {
@@ -1156,6 +1162,17 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
     return SPHB200_OK;
 }
 
+// lanes per union group in the 2nd-half kernel: 0 = one thread per group (k_second_half_tile), 2 / 4 = k_second_half_quad
+// Measured at 20.1 M particles (B200, ms per launch): fp64 tile 8.61, 2 lanes 7.99, 4 lanes 8.36; fp32 tile 3.80, 2 lanes 4.63,
+// 4 lanes 4.54 (fp32 is issue-bound: the duplicated member state and the shuffles cost more than the merged sectors give).
+template <class R>
+static int quadLanes()
+{
+    const char *e = getenv("SPHB200_QUAD"); // read per call: the parity test runs the variants in one process
+    if (!e)
+        return sizeof(R) == 8 ? SPHB_QUAD_DEFAULT_F64 : SPHB_QUAD_DEFAULT_F32;
+    return e[0] == '4' ? 4 : (e[0] == '2' ? 2 : 0);
+}
 template <int D, class R>
 static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall, int riemann, double dt_)
 {
@@ -1207,7 +1224,34 @@ static sphb200_status secondHalf(sphb200_relation *inner, sphb200_relation *wall
         UContactP<R> uw;
         SPHB_TRY((makeUContactP<D, R>(wall, wp, uw, true)));
         const int64_t n_threads = (b->own_end - U.base + G - 1) / G;
-        if (wallPrepass(wall))
+        const int quad = quadLanes<R>();
+        if (quad && kWideLanes == 1 && (!wall || wallPrepass(wall)))
+        { // QL lanes per group split the union list (tile.cuh k_second_half_quad)
+            const R *ws = nullptr;
+            const u32 *wcount = nullptr;
+            if (wall)
+            {
+                UnionList &UW = wall->lists[0].uni;
+                SPHB_TRY(ensureActive(ctx, UW));
+                SPHB_CUDA(ctx, b->wall_sum.ensure(size_t(b->n) * (D + 1) * sizeof(R)));
+                R *wsum = static_cast<R *>(b->wall_sum.p);
+                k_second_half_wall<D, R, G><<<148 * 4, 128, 0, ctx->stream>>>(UW.base, b->own_begin, b->own_end, UW.queue, rec_b, uw.t[0],
+                                                                            makeTileKernelP<R>(kern_w), R(fl.limiter_slope * fl.inv_c0_ave), wsum, fl.ctl);
+                SPHB_LAUNCH_CHECK(ctx);
+                ws = wsum;
+                wcount = uw.t[0].u.count;
+            }
+            const int64_t lanes = n_threads * quad;
+            if (quad == 4 && wall)
+                k_second_half_quad<D, R, G, 4, true><<<gridFor(lanes, 128), 128, 0, ctx->stream>>>(U.base, b->own_begin, b->own_end, n_threads, rec_b, ulistOf(U), wcount, makeTileKernelP<R>(P.kern), fl, R(dt_), pos, rho, drho, force, ws);
+            else if (quad == 4)
+                k_second_half_quad<D, R, G, 4, false><<<gridFor(lanes, 128), 128, 0, ctx->stream>>>(U.base, b->own_begin, b->own_end, n_threads, rec_b, ulistOf(U), wcount, makeTileKernelP<R>(P.kern), fl, R(dt_), pos, rho, drho, force, ws);
+            else if (wall)
+                k_second_half_quad<D, R, G, 2, true><<<gridFor(lanes, 128), 128, 0, ctx->stream>>>(U.base, b->own_begin, b->own_end, n_threads, rec_b, ulistOf(U), wcount, makeTileKernelP<R>(P.kern), fl, R(dt_), pos, rho, drho, force, ws);
+            else
+                k_second_half_quad<D, R, G, 2, false><<<gridFor(lanes, 128), 128, 0, ctx->stream>>>(U.base, b->own_begin, b->own_end, n_threads, rec_b, ulistOf(U), wcount, makeTileKernelP<R>(P.kern), fl, R(dt_), pos, rho, drho, force, ws);
+        }
+        else if (wallPrepass(wall))
         {
             UnionList &UW = wall->lists[0].uni;
             SPHB_TRY(ensureActive(ctx, UW));

@@ -587,6 +587,40 @@ def test_run_level_observables_against_the_reference_fixtures(pk, gpu):
     r = vg.taylor_green(51, backend=gpu)
     assert r["WaterBody_TotalKineticEnergy"]["dtw_ok"] and r["WaterBody_MaximumSpeed"]["dtw_ok"], r
     assert r["WaterBody_TotalKineticEnergy"]["first_sample_over_1pct"] >= 2, r@pytest.mark.gpu
+@pytest.mark.parametrize("ndim,dp,real_bytes,amp", [(3, 0.05, 8, 0.0), (3, 0.05, 8, 0.3), (3, 0.05, 4, 0.3), (2, 0.025, 8, 0.3)])
+def test_lanes_per_group_variants_of_the_second_half_agree(pk, gpu, oracle, ndim, dp, real_bytes, amp):
+    """k_second_half_quad (2 or 4 lanes split a group's union list, partial sums reduced by shuffles) against
+    k_second_half_tile (one thread per group): same pairs, another summation order - equal to rounding, and each within
+    the field tolerance of the oracle; with and without the wall"""
+    import os
+    out = {}
+    for flag in ("0", "2", "4", "oracle"):
+        os.environ["SPHB200_QUAD"] = flag if flag != "oracle" else "0"
+        try:
+            c = pk.cases.DamBreak(oracle if flag == "oracle" else gpu, ndim=ndim, dp=dp, real_bytes=real_bytes)
+            if amp:
+                jitter(c.water, amp)
+                for nm, v in seeded_state(c).items():
+                    set_field(c.water, nm, v)
+                c.water.update_cell_list()
+                c.update_configuration()
+            c.sys.integration_1st_half(c.inner, c.wall_contact, True, 1e-4)
+            c.sys.integration_2nd_half(c.inner, c.wall_contact, True, 1e-4)
+            a = {nm: field(c.water, nm) for nm in ("Position", "Density", "DensityChangeRate", "Force")}
+            c.sys.integration_2nd_half(c.inner, None, True, 1e-4)
+            b = {nm: field(c.water, nm) for nm in ("Position", "Density", "DensityChangeRate", "Force")}
+            out[flag] = (a, b)
+        finally:
+            os.environ.pop("SPHB200_QUAD", None)
+    tight = 1e-12 if real_bytes == 8 else 2e-5
+    for flag in ("2", "4"):
+        for k in (0, 1):
+            for nm in out["0"][k]:
+                assert rel_l2(out[flag][k][nm], out["0"][k][nm]) < tight, (flag, k, nm)
+                assert rel_l2(out[flag][k][nm], out["oracle"][k][nm]) < FP_TOL[real_bytes], (flag, k, nm)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("ndim,dp,real_bytes", [(3, 0.05, 8), (2, 0.025, 8), (3, 0.05, 4)])
 def test_viscous_force_with_wall(pk, gpu, oracle, ndim, dp, real_bytes):
     """row a14: ViscousForceWithWall = ViscousForce<Inner<>> + ViscousForce<Contact<Wall>> (viscous_dynamics.hpp:35-53,92-115)
