@@ -364,11 +364,13 @@ def test_twisting_column_steps_match_oracle(pk, gpu, oracle, decomposed):
 @pytest.mark.parametrize("ndim,dp", [(3, 0.05), (2, 0.025)])
 def test_wall_prepass_equals_in_kernel_wall_sums(pk, gpu, ndim, dp):
     """tile.cuh: the wall sums formed by the dense pre-pass kernels are the ones the pair kernels form themselves
-    (same arithmetic, same order): whole steps must agree bit for bit"""
+    (same arithmetic, same order): whole steps must agree bit for bit.  One thread per group in both runs
+    (SPHB200_QUAD=0): the two-lane 2nd-half kernel needs the pre-pass and sums in another order"""
     import os
     runs = []
     for flag in ("1", "0"):
         os.environ["SPHB200_WALL_PREPASS"] = flag
+        os.environ["SPHB200_QUAD"] = "0"
         try:
             c = pk.cases.DamBreak(gpu, ndim=ndim, dp=dp, real_bytes=8)
             c.sys.set_pair_kernel(1)
@@ -378,6 +380,7 @@ def test_wall_prepass_equals_in_kernel_wall_sums(pk, gpu, ndim, dp):
             runs[-1]["dt"] = c.dt
         finally:
             os.environ.pop("SPHB200_WALL_PREPASS", None)
+            os.environ.pop("SPHB200_QUAD", None)
     for nm in runs[0]:
         assert np.array_equal(runs[0][nm], runs[1][nm]), nm
 
