@@ -136,6 +136,18 @@ sphb200_status sphb200_periodic_bounding(sphb200_body *b, int axis);
 sphb200_status sphb200_relation_inner_create(sphb200_body *b, sphb200_relation **out);
 sphb200_status sphb200_relation_contact_create(sphb200_body *b, sphb200_body *const *targets, int n_targets,
                                                sphb200_relation **out);
+/* The solid-contact neighbour builders on the same cell lists.  part_original_ids (n_part > 0) restricts
+ * the SOURCE particles to a body part by particle (the reference's BodySurfaceLayer; its geometry is the caller's),
+ * the other particles get empty neighbourhoods.
+ *   self contact   : SelfSurfaceContactRelation + NeighborBuilderSelfContact (inner_body_relation.cpp:50-75,
+ *                    neighborhood.cpp:123-142): j is a neighbour iff |x_i - x_j| < rc and |X_i - X_j| > rc, X = the
+ *                    body's "InitialPosition" variable
+ *   surface contact: SurfaceContactRelation + NeighborBuilderSurfaceContact (contact_body_relation.cpp:192-240,
+ *                    neighborhood.cpp:162-168): the contact builder with the Wendland kernel of the AVERAGED smoothing
+ *                    length, cut-off 2 * 0.5 * (h_source + h_target) */
+sphb200_status sphb200_relation_self_contact_create(sphb200_body *b, const int64_t *part_original_ids, int64_t n_part, sphb200_relation **out);
+sphb200_status sphb200_relation_surface_contact_create(sphb200_body *b, sphb200_body *const *targets, int n_targets,
+                                                       const int64_t *part_original_ids, int64_t n_part, sphb200_relation **out);
 /* SPHRelation::updateConfiguration (base_body_relation.h:100; searchNeighborsByMesh
  * meshes/cell_linked_list.hpp:20-46 with NeighborBuilderInner/Contact neighborhood.cpp:85-98,147-160).
  * Builds a compact u32 neighbour-index list (count → scan → fill, cf. CK update_body_relation.hpp:117-164). */
@@ -208,6 +220,20 @@ sphb200_status sphb200_maximum_speed(sphb200_body *b, double *out);
 sphb200_status sphb200_position_bound(sphb200_body *b, int upper, double *out3);
 /* ObservingAQuantity (general_dynamics/general_interpolation.h:63-83): out = n_observer*width doubles */
 sphb200_status sphb200_observe(sphb200_relation *contact, const char *name, int width, double *out);
+
+/* ---- CK-flavour fluid dynamics of the reference's SYCL dam-break tests ------------------ */
+/* All three evaluate W / dW with the CK smoothing kernel, the 20-interval cubic-Lagrange table of Wendland C2
+ * (shared_ck/smoothing_kernel/kernel_tabulated_ck.h:37-71; inv_h = 1 / max(h_source, h_target), neighbor_method.hpp:73-120).
+ * CompressionSummation<Inner, Contact> + DensityRegularization<FreeSurface | Internal>
+ * (shared_ck/particle_dynamics/fluid_dynamics/density_regularization.hpp:42-111): CompressionSummation = W0 Vref_i + sum W_ij Vref_j,
+ * Compression = max(sum, 1) | sum, Density = Compression * rho0; "VolumetricMeasureRef" is copied from VolumetricMeasure when first used */
+sphb200_status sphb200_ck_density_regularization(sphb200_relation *inner, sphb200_relation *contact_or_null, int free_surface);
+/* LinearCorrectionMatrix<Inner<WithUpdate>>(alpha) + <Contact> (general_dynamics/kernel_correction_ck.hpp:36-96): B = -sum r_ij (nablaW_ij V_j)^T,
+ * then B <- w B^-1(Tikhonov, 1e-8) + (1 - w) I with w = det / (det + max(alpha - det, 0)); variable "LinearCorrectionMatrix" (ndim x ndim) */
+sphb200_status sphb200_ck_linear_correction_matrix(sphb200_relation *inner, sphb200_relation *contact_or_null, double alpha);
+/* FreeSurfaceIndicationCK<Inner<WithUpdate>> + <Contact> (general_dynamics/surface_indication/surface_indication_ck.hpp:55-170): variables
+ * "PositionDivergence", "Indicator", "PreviousSurfaceIndicator" (the reference's int variables are Real-typed 0 / 1 here) */
+sphb200_status sphb200_ck_free_surface_indication(sphb200_relation *inner, sphb200_relation *contact_or_null);
 
 /* ---- total-Lagrangian elastic solid -------------------------------------------------------- */
 /* LinearGradientCorrectionMatrix<Inner<>> (general_dynamics/kernel_correction.cpp:8-29) */

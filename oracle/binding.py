@@ -36,6 +36,7 @@ def load():
         "orc_update_cell_list": (None, [vp, i]), "orc_periodic_bounding": (None, [vp, i, i]),
         "orc_periodic_cell_list": (None, [vp, i, i]), "orc_sort": (None, [vp, i]),
         "orc_relation_inner": (i, [vp, i]), "orc_relation_contact": (i, [vp, i, ip, i]),
+        "orc_relation_self_contact": (i, [vp, i, lp, l]), "orc_relation_surface_contact": (i, [vp, i, ip, i, lp, l]),
         "orc_relation_update": (None, [vp, i]), "orc_neighbors": (l, [vp, i, i, ip, lp]),
         "orc_search_depth": (i, [vp, i, i]),
         "orc_density_summation": (None, [vp, i, i, i]),
@@ -44,7 +45,8 @@ def load():
         "orc_gravity_force": (None, [vp, i, dp]), "orc_viscous_force": (None, [vp, i, i]),
         "orc_transport_velocity_correction": (None, [vp, i, d]),
         "orc_total_kinetic_energy": (d, [vp, i]), "orc_total_mechanical_energy": (d, [vp, i, dp]),
-        "orc_maximum_speed": (d, [vp, i]), "orc_position_bound": (None, [vp, i, i, dp]), "orc_observe": (None, [vp, i, cp, i, dp]),
+        "orc_ck_density_regularization": (None, [vp, i, i, i]), "orc_ck_linear_correction_matrix": (None, [vp, i, i, d]),
+        "orc_ck_free_surface_indication": (None, [vp, i, i]), "orc_maximum_speed": (d, [vp, i]), "orc_position_bound": (None, [vp, i, i, dp]), "orc_observe": (None, [vp, i, cp, i, dp]),
         "orc_correction_matrix": (None, [vp, i]), "orc_solid_1st_half": (None, [vp, i, i, d]),
         "orc_solid_2nd_half": (None, [vp, i, d]), "orc_solid_constrain": (None, [vp, i, lp, l]),
         "orc_solid_dt": (d, [vp, i, d]), "orc_num_threads": (i, []), "orc_set_num_threads": (i, [i]),
@@ -98,6 +100,12 @@ class SPHSystem:
     def contact(self, body, targets):
         return Relation(self, body, list(targets))
 
+    def self_contact(self, body, part_ids=None):
+        return Relation(self, body, None, builder="self", part_ids=part_ids)
+
+    def surface_contact(self, body, targets, part_ids=None):
+        return Relation(self, body, list(targets), builder="surface", part_ids=part_ids)
+
     def _g3(self, g):
         return (C.c_double * 3)(*list(g) + [0.0] * (3 - len(g)))
 
@@ -124,6 +132,15 @@ class SPHSystem:
 
     def transport_velocity_correction(self, inner, coefficient=0.2):
         self.lib.orc_transport_velocity_correction(self.h, inner.id, coefficient)
+
+    def ck_density_regularization(self, inner, contact=None, free_surface=True):
+        self.lib.orc_ck_density_regularization(self.h, inner.id, contact.id if contact else -1, int(free_surface))
+
+    def ck_linear_correction_matrix(self, inner, contact=None, alpha=0.0):
+        self.lib.orc_ck_linear_correction_matrix(self.h, inner.id, contact.id if contact else -1, alpha)
+
+    def ck_free_surface_indication(self, inner, contact=None):
+        self.lib.orc_ck_free_surface_indication(self.h, inner.id, contact.id if contact else -1)
 
     def total_kinetic_energy(self, body):
         return self.lib.orc_total_kinetic_energy(self.h, body.id)
@@ -236,9 +253,16 @@ class Body:
 
 
 class Relation:
-    def __init__(self, system, body, targets):
+    def __init__(self, system, body, targets, builder=None, part_ids=None):
         self.sys, self.lib, self.body, self.targets = system, system.lib, body, targets
-        if targets is None:
+        ids = np.ascontiguousarray(part_ids if part_ids is not None else [], dtype=np.int64)
+        idp = ids.ctypes.data_as(C.POINTER(C.c_long)) if ids.size else None
+        if builder == "self":
+            self.id = self.lib.orc_relation_self_contact(system.h, body.id, idp, ids.size)
+        elif builder == "surface":
+            arr = (C.c_int * len(targets))(*[t.id for t in targets])
+            self.id = self.lib.orc_relation_surface_contact(system.h, body.id, arr, len(targets), idp, ids.size)
+        elif targets is None:
             self.id = self.lib.orc_relation_inner(system.h, body.id)
         else:
             arr = (C.c_int * len(targets))(*[t.id for t in targets])

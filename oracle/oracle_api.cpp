@@ -3,6 +3,7 @@
 // handles are small integers.  Runtime dispatch over (ndim, real_bytes).
 #include "oracle_fluid.hpp"
 #include "oracle_solid.hpp"
+#include "oracle_ck.hpp"
 #include <cstdio>
 #ifdef _OPENMP
 #include <omp.h>
@@ -237,6 +238,38 @@ int orc_relation_contact(void *sys, int body, const int *targets, int n_targets)
     });
     return id;
 }
+// SelfSurfaceContactRelation / SurfaceContactRelation over a body part by particle (original ids; n_part = 0: all)
+int orc_relation_self_contact(void *sys, int body, const long *part, long n_part)
+{
+    int id = orc_relation_inner(sys, body);
+    DISPATCH(sys, {
+        auto &r = *S.rels[id];
+        r.builder = 1;
+        if (n_part > 0)
+        {
+            r.part.assign(r.body->n, 0);
+            for (long k = 0; k < n_part; ++k)
+                r.part[size_t(part[k])] = 1;
+        }
+    });
+    return id;
+}
+int orc_relation_surface_contact(void *sys, int body, const int *targets, int n_targets, const long *part, long n_part)
+{
+    int id = orc_relation_contact(sys, body, targets, n_targets);
+    DISPATCH(sys, {
+        auto &r = *S.rels[id];
+        r.builder = 2;
+        setupRelation<D, R>(r);
+        if (n_part > 0)
+        {
+            r.part.assign(r.body->n, 0);
+            for (long k = 0; k < n_part; ++k)
+                r.part[size_t(part[k])] = 1;
+        }
+    });
+    return id;
+}
 void orc_relation_update(void *sys, int rel) { DISPATCH(sys, updateRelation<D, R>(*S.rels[rel])); }
 // neighbour dump: counts[n]; if j_out != null, flat concatenation in list order (k-th target)
 long orc_neighbors(void *sys, int rel, int k, int *counts, long *j_out)
@@ -303,6 +336,18 @@ void orc_viscous_force(void *sys, int inner, int wall)
 void orc_transport_velocity_correction(void *sys, int inner, double coeff)
 {
     DISPATCH(sys, transportVelocityCorrection<D, R>(*S.rels[inner], R(coeff)));
+}
+void orc_ck_density_regularization(void *sys, int inner, int contact, int free_surface)
+{
+    DISPATCH(sys, compressionRegularization<D, R>(*S.rels[inner], contact >= 0 ? S.rels[contact].get() : nullptr, free_surface != 0));
+}
+void orc_ck_linear_correction_matrix(void *sys, int inner, int contact, double alpha)
+{
+    DISPATCH(sys, linearCorrectionMatrixCK<D, R>(*S.rels[inner], contact >= 0 ? S.rels[contact].get() : nullptr, R(alpha)));
+}
+void orc_ck_free_surface_indication(void *sys, int inner, int contact)
+{
+    DISPATCH(sys, freeSurfaceIndicationCK<D, R>(*S.rels[inner], contact >= 0 ? S.rels[contact].get() : nullptr));
 }
 void orc_position_bound(void *sys, int body, int upper, double *out3)
 {

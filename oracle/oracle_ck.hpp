@@ -1,0 +1,261 @@
+// ORACLE - TEST INFRASTRUCTURE ONLY (see oracle_core.hpp header).
+// CK-flavour local dynamics of the SYCL dam-break tests, restated per particle:
+//   smoothing kernel        shared_ck/smoothing_kernel/kernel_tabulated_ck.h:37-71, .cpp:6-27 (20-interval cubic Lagrange table of
+//                           Wendland C2), shared_ck/body_relation/neighbor_method.hpp:17-52,73-120 (inv_h = 1 / max(h_src, h_tar))
+//   CompressionSummation + DensityRegularization   shared_ck/particle_dynamics/fluid_dynamics/density_regularization.hpp:42-111, .h:146-180
+//   LinearCorrectionMatrix<Inner<WithUpdate>> + <Contact>   shared_ck/particle_dynamics/general_dynamics/kernel_correction_ck.hpp:36-96,
+//                           common/vector_functions.h:198-203 (inverseTikhonov)
+//   FreeSurfaceIndicationCK<Inner<WithUpdate>> + <Contact>  .../surface_indication/surface_indication_ck.hpp:55-170
+// Neighbours are the relation's index sets; W, dW are re-evaluated with the tabulated kernel from the particle positions,
+// as the CK kernels do (they store indices only).
+#pragma once
+#include "oracle_core.hpp"
+#include "oracle_solid.hpp"
+
+namespace orc
+{
+template <int D, class R>
+struct TabKernel
+{
+    static constexpr int res = 20, size = 24;
+    R dq, dq0, dq1, dq2, dq3, w[size], dw[size], dimfac, inv_h, src_inv_h;
+    TabKernel(R h_src, R h_tar)
+    {
+        const R kernel_size = R(2.0);
+        dq = kernel_size / R(res);
+        for (int i = 0; i < size; ++i)
+        {
+            const R q = R(i - 1) * dq;
+            w[i] = R(std::pow(R(1.0) - R(0.5) * q, 4)) * (R(1.0) + R(2.0) * q);
+            dw[i] = R(0.625) * R(std::pow(q - R(2.0), 3)) * q;
+        }
+        dq0 = (R(-1.0) * dq) * (R(-2.0) * dq) * (R(-3.0) * dq);
+        dq1 = dq * (R(-1.0) * dq) * (R(-2.0) * dq);
+        dq2 = (R(2.0) * dq) * dq * (R(-1.0) * dq);
+        dq3 = (R(3.0) * dq) * (R(2.0) * dq) * dq;
+        // DimensionFactor = factor_W * h^D (base_kernel.h:91-93) with kernel_wendland_c2.cpp:11-13
+        const R h = h_src, ih = R(1.0) / h;
+        dimfac = D == 2 ? (ih * ih * R(7.0) / (R(4.0) * R(kPi))) * h * h : (ih * ih * ih * R(21.0) / (R(16.0) * R(kPi))) * h * h * h;
+        src_inv_h = R(1.0) / h_src;
+        inv_h = R(1.0) / std::max(h_src, h_tar);
+    }
+    R cubic(const R *data, R q) const
+    {
+        const int location = int(std::floor(q / dq));
+        const int i = location + 1;
+        const R f1 = q - R(location) * dq, f0 = f1 + dq, f2 = f1 - dq, f3 = f1 - R(2) * dq;
+        return (f1 * f2 * f3) / dq0 * data[i - 1] + (f0 * f2 * f3) / dq1 * data[i] + (f0 * f1 * f3) / dq2 * data[i + 1] +
+               (f0 * f1 * f2) / dq3 * data[i + 2];
+    }
+    R ipow(R x, int n) const
+    {
+        R r = R(1);
+        for (int k = 0; k < n; ++k)
+            r *= x;
+        return r;
+    }
+    R W0() const { return ipow(src_inv_h, D) * dimfac * cubic(w, R(0)); }
+    R W(R r) const { return ipow(inv_h, D) * dimfac * cubic(w, r * inv_h); }
+    R dW(R r) const { return ipow(inv_h, D + 1) * dimfac * cubic(dw, r * inv_h); }
+};
+
+template <int D, class R>
+inline R dispNorm(const R *xi, const R *xj, R *d)
+{
+    for (int a = 0; a < D; ++a)
+        d[a] = xi[a] - xj[a];
+    return std::sqrt(sqnorm<D, R>(d));
+}
+
+// registerStateVariableFrom<Real>("VolumetricMeasureRef", "VolumetricMeasure"): a copy taken when first registered
+template <int D, class R>
+inline R *volRef(Body<D, R> &b)
+{
+    const bool fresh = b.vars.find("VolumetricMeasureRef") == b.vars.end();
+    R *ref = b.v("VolumetricMeasureRef", 1);
+    if (fresh)
+    {
+        b.evolving("VolumetricMeasureRef");
+        const R *vol = b.v("VolumetricMeasure");
+        for (size_t i = 0; i < b.n; ++i)
+            ref[i] = vol[i];
+    }
+    return ref;
+}
+
+template <int D, class R>
+void compressionRegularization(Relation<D, R> &inner, Relation<D, R> *contact, bool free_surface)
+{
+    Body<D, R> &b = *inner.body;
+    const R *pos = b.v("Position", D);
+    R *vref = volRef<D, R>(b), *csum = b.v("CompressionSummation"), *comp = b.v("Compression"), *rho = b.v("Density");
+    const TabKernel<D, R> k(b.h, b.h);
+    const long n = long(b.n);
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < n; ++i)
+    {
+        R s = k.W0() * vref[i];
+        const auto &nb = inner.configs[0][i];
+        for (size_t m = 0; m != nb.current_size; ++m)
+        {
+            R d[D];
+            s += k.W(dispNorm<D, R>(pos + i * D, pos + nb.j[m] * D, d)) * vref[nb.j[m]];
+        }
+        csum[i] = s;
+    }
+    if (contact)
+        for (size_t t = 0; t < contact->targets.size(); ++t)
+        {
+            Body<D, R> &tb = *contact->targets[t];
+            const R *tpos = tb.v("Position", D);
+            const R *tref = volRef<D, R>(tb);
+            const TabKernel<D, R> kc(b.h, tb.h);
+#pragma omp parallel for schedule(static)
+            for (long i = 0; i < n; ++i)
+            {
+                const auto &cn = contact->configs[t][i];
+                for (size_t m = 0; m != cn.current_size; ++m)
+                {
+                    R d[D];
+                    csum[i] += kc.W(dispNorm<D, R>(pos + i * D, tpos + cn.j[m] * D, d)) * tref[cn.j[m]];
+                }
+            }
+        }
+    for (long i = 0; i < n; ++i)
+    {
+        comp[i] = free_surface ? std::max(csum[i], R(1)) : csum[i];
+        rho[i] = comp[i] * R(b.mat.rho0);
+    }
+}
+
+template <int D, class R>
+void linearCorrectionMatrixCK(Relation<D, R> &inner, Relation<D, R> *contact, R alpha)
+{
+    Body<D, R> &b = *inner.body;
+    const R *pos = b.v("Position", D), *vol = b.v("VolumetricMeasure");
+    R *B = b.v("LinearCorrectionMatrix", D * D);
+    const TabKernel<D, R> k(b.h, b.h);
+    const long n = long(b.n);
+    auto accumulate = [&](long i, const R *xj, R Vj, const TabKernel<D, R> &kk)
+    {
+        R d[D];
+        const R r = dispNorm<D, R>(pos + i * D, xj, d);
+        const R dw = kk.dW(r);
+        for (int a = 0; a < D; ++a)
+            for (int c = 0; c < D; ++c)
+                B[i * D * D + a * D + c] -= d[a] * ((dw * (d[c] / r)) * Vj); // vec_r_ij * (nablaW_ij V_j)^T
+    };
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < n; ++i)
+    {
+        for (int q = 0; q < D * D; ++q)
+            B[i * D * D + q] = R(0);
+        const auto &nb = inner.configs[0][i];
+        for (size_t m = 0; m != nb.current_size; ++m)
+            accumulate(i, pos + nb.j[m] * D, vol[nb.j[m]], k);
+    }
+    if (contact)
+        for (size_t t = 0; t < contact->targets.size(); ++t)
+        {
+            Body<D, R> &tb = *contact->targets[t];
+            const R *tpos = tb.v("Position", D), *tvol = tb.v("VolumetricMeasure");
+            const TabKernel<D, R> kc(b.h, tb.h);
+#pragma omp parallel for schedule(static)
+            for (long i = 0; i < n; ++i)
+            {
+                const auto &cn = contact->configs[t][i];
+                for (size_t m = 0; m != cn.current_size; ++m)
+                    accumulate(i, tpos + cn.j[m] * D, tvol[cn.j[m]], kc);
+            }
+        }
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < n; ++i)
+    {
+        Mat<D, R> M = Mat<D, R>::load(B + i * D * D);
+        const R det = M.det();
+        const R det_sqr = std::max(alpha - det, R(0));
+        Mat<D, R> Mt = M.T();
+        Mat<D, R> inv = (Mt * M + Mat<D, R>::identity() * R(1.0e-8)).inverse() * Mt;
+        const R weight = det / (det + det_sqr);
+        (inv * weight + Mat<D, R>::identity() * (R(1.0) - weight)).store(B + i * D * D);
+    }
+}
+
+// Indicator / PreviousSurfaceIndicator are int variables in the reference; here Real-typed 0 / 1
+template <int D, class R>
+void freeSurfaceIndicationCK(Relation<D, R> &inner, Relation<D, R> *contact)
+{
+    Body<D, R> &b = *inner.body;
+    const R *pos = b.v("Position", D), *vol = b.v("VolumetricMeasure");
+    const bool fresh = b.vars.find("PreviousSurfaceIndicator") == b.vars.end();
+    R *ind = b.v("Indicator"), *pdiv = b.v("PositionDivergence"), *prev = b.v("PreviousSurfaceIndicator", 1);
+    const long n = long(b.n);
+    if (fresh)
+    {
+        b.evolving("PreviousSurfaceIndicator");
+        for (long i = 0; i < n; ++i)
+            prev[i] = R(1);
+    }
+    const TabKernel<D, R> k(b.h, b.h);
+    const R threshold = R(0.75) * R(D), h = b.h;
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < n; ++i)
+    {
+        R pd = R(0);
+        bool near_prev = false;
+        const auto &nb = inner.configs[0][i];
+        for (size_t m = 0; m != nb.current_size; ++m)
+        {
+            R d[D];
+            const R r = dispNorm<D, R>(pos + i * D, pos + nb.j[m] * D, d);
+            pd -= k.dW(r) * vol[nb.j[m]] * r;
+            near_prev = near_prev || prev[nb.j[m]] == R(1);
+        }
+        if (pd < threshold && prev[i] != R(1) && !near_prev)
+            pd = R(2.0) * threshold;
+        pdiv[i] = pd;
+    }
+    if (contact)
+        for (size_t t = 0; t < contact->targets.size(); ++t)
+        {
+            Body<D, R> &tb = *contact->targets[t];
+            const R *tpos = tb.v("Position", D), *tvol = tb.v("VolumetricMeasure");
+            const TabKernel<D, R> kc(b.h, tb.h);
+#pragma omp parallel for schedule(static)
+            for (long i = 0; i < n; ++i)
+            {
+                R pd = R(0);
+                const auto &cn = contact->configs[t][i];
+                for (size_t m = 0; m != cn.current_size; ++m)
+                {
+                    R d[D];
+                    const R r = dispNorm<D, R>(pos + i * D, tpos + cn.j[m] * D, d);
+                    pd -= kc.dW(r) * tvol[cn.j[m]] * r;
+                }
+                pdiv[i] += pd;
+            }
+        }
+    std::vector<R> out(static_cast<size_t>(n));
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < n; ++i)
+    {
+        R v = R(1);
+        if (pdiv[i] > threshold)
+        {
+            bool very_near = false;
+            const auto &nb = inner.configs[0][i];
+            for (size_t m = 0; m != nb.current_size && !very_near; ++m)
+            {
+                R d[D];
+                const R r = dispNorm<D, R>(pos + i * D, pos + nb.j[m] * D, d);
+                very_near = pdiv[nb.j[m]] < threshold && r < h;
+            }
+            if (!very_near)
+                v = R(0);
+        }
+        out[size_t(i)] = v;
+    }
+    for (long i = 0; i < n; ++i)
+        ind[i] = prev[i] = out[size_t(i)];
+}
+} // namespace orc

@@ -304,11 +304,15 @@ inline R sqnorm(const R *d)
 
 // searchNeighborsByMesh: meshes/cell_linked_list.hpp:20-46 with NeighborBuilderInner
 // (particle_neighborhood/neighborhood.cpp:85-98) or NeighborBuilderContact (:147-160).
+// builder 1: NeighborBuilderSelfContact (neighborhood.cpp:123-142), part: the body part's particles (current indices
+// flagged through original ids), others keep empty neighbourhoods (inner_body_relation.cpp:57-75)
 template <int D, class R>
 void searchNeighbors(Body<D, R> &src, Body<D, R> &tgt, const Kernel<D, R> &kernel, int depth, bool inner,
-                     std::vector<Neighborhood<D, R>> &cfg)
+                     std::vector<Neighborhood<D, R>> &cfg, int builder = 0, const std::vector<unsigned char> *part = nullptr)
 {
     const R *pos = src.v("Position", D);
+    const R *pos0_s = builder == 1 ? src.v("InitialPosition", D) : nullptr;
+    const R *pos0_t = builder == 1 ? tgt.v("InitialPosition", D) : nullptr;
     cfg.resize(src.n);
     const Mesh<D, R> &mesh = tgt.mesh;
 #pragma omp parallel for schedule(dynamic, 256)
@@ -317,6 +321,8 @@ void searchNeighbors(Body<D, R> &src, Body<D, R> &tgt, const Kernel<D, R> &kerne
         size_t i = size_t(ii);
         Neighborhood<D, R> &nb = cfg[i];
         nb.current_size = 0;
+        if (part && !(*part)[src.original_id[i]])
+            continue;
         int c[D], lo[D], hi[D];
         mesh.cellIndex(pos + i * D, c);
         for (int d = 0; d < D; ++d)
@@ -338,7 +344,15 @@ void searchNeighbors(Body<D, R> &src, Body<D, R> &tgt, const Kernel<D, R> &kerne
                         for (int d = 0; d < D; ++d)
                             dsp[d] = pos[i * D + d] - entry.second[d];
                         R metric = sqnorm<D, R>(dsp);
-                        if (metric < kernel.rc2 && (!inner || i != j))
+                        bool accept = metric < kernel.rc2 && (!inner || i != j);
+                        if (builder == 1)
+                        {
+                            R d0[D];
+                            for (int d = 0; d < D; ++d)
+                                d0[d] = pos0_s[i * D + d] - pos0_t[j * D + d];
+                            accept = std::sqrt(metric) < kernel.rc && std::sqrt(sqnorm<D, R>(d0)) > kernel.rc;
+                        }
+                        if (accept)
                         {
                             R dist = std::sqrt(metric);
                             R e[D];
@@ -361,6 +375,8 @@ struct Relation
     std::vector<std::vector<Neighborhood<D, R>>> configs;
     std::vector<Kernel<D, R>> kernels;
     std::vector<int> depths;
+    int builder = 0; // 0 inner / contact, 1 self contact, 2 surface contact
+    std::vector<unsigned char> part; // by original id; empty: all particles
 };
 
 // body_relations/inner_body_relation.cpp:14-20; contact_body_relation.cpp:22-32;
@@ -380,7 +396,10 @@ void setupRelation(Relation<D, R> &rel)
     rel.configs.resize(rel.targets.size());
     for (auto *t : rel.targets)
     {
-        rel.kernels.push_back(rel.body->kernel.h > t->kernel.h ? rel.body->kernel : t->kernel);
+        if (rel.builder == 2) // NeighborBuilderSurfaceContact, neighborhood.cpp:162-168
+            rel.kernels.push_back(Kernel<D, R>(R(0.5) * (rel.body->kernel.h + t->kernel.h)));
+        else
+            rel.kernels.push_back(rel.body->kernel.h > t->kernel.h ? rel.body->kernel : t->kernel);
         R inv_grid_spacing = R(1.0) / t->mesh.spacing;
         rel.depths.push_back(1 + int(std::floor(rel.body->kernel.rc * inv_grid_spacing)));
     }
@@ -389,11 +408,12 @@ void setupRelation(Relation<D, R> &rel)
 template <int D, class R>
 void updateRelation(Relation<D, R> &rel)
 {
+    const std::vector<unsigned char> *part = rel.part.empty() ? nullptr : &rel.part;
     if (rel.inner)
-        searchNeighbors<D, R>(*rel.body, *rel.body, rel.kernels[0], 1, true, rel.configs[0]);
+        searchNeighbors<D, R>(*rel.body, *rel.body, rel.kernels[0], 1, rel.builder != 1, rel.configs[0], rel.builder, part);
     else
         for (size_t k = 0; k < rel.targets.size(); ++k)
-            searchNeighbors<D, R>(*rel.body, *rel.targets[k], rel.kernels[k], rel.depths[k], false, rel.configs[k]);
+            searchNeighbors<D, R>(*rel.body, *rel.targets[k], rel.kernels[k], rel.depths[k], false, rel.configs[k], rel.builder, part);
 }
 
 } // namespace orc

@@ -59,6 +59,8 @@ SIGNATURES = {
     "sphb200_periodic_bounding": (_i, [_vp, _i]),
     "sphb200_relation_inner_create": (_i, [_vp, _vpp]),
     "sphb200_relation_contact_create": (_i, [_vp, _vpp, _i, _vpp]),
+    "sphb200_relation_self_contact_create": (_i, [_vp, _i64p, _i64, _vpp]),
+    "sphb200_relation_surface_contact_create": (_i, [_vp, _vpp, _i, _i64p, _i64, _vpp]),
     "sphb200_relation_update": (_i, [_vp]),
     "sphb200_relation_neighbors": (_i, [_vp, _i, C.POINTER(C.c_int32), _i64p, _i64p]),
     "sphb200_relation_stats": (_i, [_vp, _i, _dp]),
@@ -85,6 +87,9 @@ SIGNATURES = {
     "sphb200_maximum_speed": (_i, [_vp, _dp]),
     "sphb200_position_bound": (_i, [_vp, _i, _dp]),
     "sphb200_observe": (_i, [_vp, _cp, _i, _dp]),
+    "sphb200_ck_density_regularization": (_i, [_vp, _vp, _i]),
+    "sphb200_ck_linear_correction_matrix": (_i, [_vp, _vp, _d]),
+    "sphb200_ck_free_surface_indication": (_i, [_vp, _vp]),
     "sphb200_correction_matrix": (_i, [_vp]),
     "sphb200_solid_1st_half": (_i, [_vp, _i, _d]),
     "sphb200_solid_2nd_half": (_i, [_vp, _d]),

@@ -312,6 +312,11 @@ struct sphb200_relation
     std::vector<uint64_t> target_stamp;
     uint64_t source_stamp = 0;
     bool valid = false;
+    // neighbour builder (particle_neighborhood/neighborhood.cpp): 0 NeighborBuilderInner / Contact, 1 SelfContact
+    // (:123-142: r < rc and r0 > rc on InitialPosition), 2 SurfaceContact (:162-168: kernel of the averaged smoothing length)
+    int builder = 0;
+    sphb::DevBuf part_flag; // u8 per ORIGINAL id: the source particles of a body part (BodySurfaceLayer); empty = all
+    bool has_part = false;
 };
 
 namespace sphb

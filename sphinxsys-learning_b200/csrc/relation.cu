@@ -28,6 +28,11 @@ struct SearchP
     R rc;
     int depth;
     int inner;
+    // other neighbour builders (generic search only)
+    int builder;               // 0 inner / contact, 1 self contact, 2 surface contact (rc of the averaged kernel)
+    const unsigned char *part; // source particles of a body part, by original id; null: every particle
+    const u32 *oid_s;          // OriginalID of the source body
+    const R *pos0_s, *pos0_t;  // InitialPosition (self contact)
 };
 
 // Calls f(j, xj_shifted) for every candidate entry of the 3^d (depth) cell block around xi,
@@ -178,7 +183,7 @@ __global__ void __launch_bounds__(128) k_search(int64_t n_src, const typename Re
     int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     const int lane = threadIdx.x & 31;
     u32 cnt = 0;
-    if (i < n_src)
+    if (i < n_src && (!sp.part || sp.part[sp.oid_s[i]]))
     {
         typename Real4<R>::type v = ldg4(xV_s + i);
         R xi[D];
@@ -197,7 +202,16 @@ __global__ void __launch_bounds__(128) k_search(int64_t n_src, const typename Re
                                    for (int a = 0; a < D; ++a)
                                        d[a] = xi[a] - xj[a];
                                    R m = sqnormExact<D, R>(d);
-                                   if (m < sp.rc2 && (!sp.inner || j != u32(i)))
+                                   bool accept = m < sp.rc2 && (!sp.inner || j != u32(i));
+                                   if (sp.builder == 1)
+                                   { // NeighborBuilderSelfContact (neighborhood.cpp:123-142): distance < rc and initial distance > rc
+                                       R d0[D];
+#pragma unroll
+                                       for (int a = 0; a < D; ++a)
+                                           d0[a] = sp.pos0_s[i * D + a] - sp.pos0_t[size_t(j) * D + a];
+                                       accept = sqrt_r(m) < sp.rc && sqrt_r(sqnormExact<D, R>(d0)) > sp.rc;
+                                   }
+                                   if (accept)
                                    {
                                        if (FILL)
                                            slot0[size_t(cnt / kS) * 32u + (cnt % kS)] = j;
@@ -622,10 +636,28 @@ static sphb200_status relationUpdate(sphb200_relation *r)
         sp.mesh = Pt.mesh;
         sp.per = Pt.per;
         sp.inner = r->inner ? 1 : 0;
+        sp.builder = r->builder;
+        sp.part = r->has_part ? static_cast<const unsigned char *>(r->part_flag.p) : nullptr;
+        sp.oid_s = static_cast<const u32 *>(src->original_id.p);
+        sp.pos0_s = sp.pos0_t = nullptr;
+        if (r->builder == 1)
+        {
+            Var *p0 = src->find("InitialPosition");
+            if (!p0 || p0->width != D)
+                return ctx->fail(SPHB200_ERR_INVALID, "self-contact relation: the body has no InitialPosition variable");
+            sp.pos0_s = sp.pos0_t = static_cast<const R *>(p0->dev.p);
+            sp.inner = 0; // NeighborBuilderSelfContact has no i != j test: r0 = 0 fails r0 > rc
+        }
         // neighborhood.cpp:75-80 chooseKernel: the kernel with the larger smoothing length
         const KernelP<R> &kern = (r->inner || Ps.h > Pt.h) ? Ps.kern : Pt.kern;
         sp.rc = kern.rc;
         sp.rc2 = kern.rc2;
+        if (r->builder == 2)
+        { // NeighborBuilderSurfaceContact: KernelWendlandC2(0.5 * (h_source + h_target)), cut-off 2 h
+            const R h_avg = R(0.5) * (Ps.h + Pt.h);
+            sp.rc = R(2.0) * h_avg;
+            sp.rc2 = sp.rc * sp.rc;
+        }
         // smallest depth whose cell block covers the cut-off sphere; the reference searches
         // 1+floor(rc/spacing) cells (base_body_relation.cpp:10-16), a superset with the same accepted set
         sp.depth = 1;
@@ -645,7 +677,7 @@ static sphb200_status relationUpdate(sphb200_relation *r)
         const u32 *off = static_cast<const u32 *>(tgt->cell_offset.p);
         unsigned long long *acc = static_cast<unsigned long long *>(ctx->reduce_dev.p) + 8;
         int *overflow = reinterpret_cast<int *>(acc + 1);
-        bool fast = Pt.per.mask == 0 && sp.depth == 1;
+        bool fast = Pt.per.mask == 0 && sp.depth == 1 && r->builder == 0 && !r->has_part;
         u32 *mask = nullptr;
         for (int attempt = 0; attempt < 2; ++attempt)
         {
@@ -771,6 +803,43 @@ sphb200_status sphb200_relation_contact_create(sphb200_body *b, sphb200_body *co
     b->ctx->relations.push_back(r);
     *out = r;
     return SPHB200_OK;
+}
+
+static sphb200_status setPart(sphb200_relation *r, const int64_t *part_original_ids, int64_t n_part)
+{
+    sphb200_ctx *ctx = r->ctx;
+    r->has_part = false;
+    if (!part_original_ids || n_part <= 0)
+        return SPHB200_OK;
+    std::vector<unsigned char> flag(size_t(r->body->n), 0);
+    for (int64_t k = 0; k < n_part; ++k)
+    {
+        if (part_original_ids[k] < 0 || part_original_ids[k] >= r->body->n)
+            return ctx->fail(SPHB200_ERR_INVALID, "relation: body-part particle id out of range");
+        flag[size_t(part_original_ids[k])] = 1;
+    }
+    SPHB_CUDA(ctx, r->part_flag.ensure(flag.size()));
+    SPHB_CUDA(ctx, cudaMemcpyAsync(r->part_flag.p, flag.data(), flag.size(), cudaMemcpyHostToDevice, ctx->stream));
+    SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    r->has_part = true;
+    return SPHB200_OK;
+}
+
+sphb200_status sphb200_relation_self_contact_create(sphb200_body *b, const int64_t *part_original_ids, int64_t n_part, sphb200_relation **out)
+{
+    SPHB_TRY(sphb200_relation_inner_create(b, out));
+    (*out)->builder = 1;
+    cudaSetDevice(b->ctx->device);
+    return setPart(*out, part_original_ids, n_part);
+}
+
+sphb200_status sphb200_relation_surface_contact_create(sphb200_body *b, sphb200_body *const *targets, int n_targets,
+                                                       const int64_t *part_original_ids, int64_t n_part, sphb200_relation **out)
+{
+    SPHB_TRY(sphb200_relation_contact_create(b, targets, n_targets, out));
+    (*out)->builder = 2;
+    cudaSetDevice(b->ctx->device);
+    return setPart(*out, part_original_ids, n_part);
 }
 
 sphb200_status sphb200_relation_update(sphb200_relation *r)

@@ -98,6 +98,18 @@ class SPHSystem:
         self.relations.append(r)
         return r
 
+    def self_contact(self, body, part_ids=None):
+        """SelfSurfaceContactRelation over a body part by particle (original ids), or the whole body"""
+        r = Relation(self, body, None, builder="self", part_ids=part_ids)
+        self.relations.append(r)
+        return r
+
+    def surface_contact(self, body, targets, part_ids=None):
+        """SurfaceContactRelation: contact builder with the kernel of the averaged smoothing length"""
+        r = Relation(self, body, list(targets), builder="surface", part_ids=part_ids)
+        self.relations.append(r)
+        return r
+
     def exclusive_scan(self, values):
         v = np.ascontiguousarray(values, dtype=np.uint32)
         out = np.zeros_like(v)
@@ -178,6 +190,15 @@ class SPHSystem:
 
     def transport_velocity_correction(self, inner, coefficient=0.2):
         self.check(self.lib.sphb200_transport_velocity_correction(inner.h, coefficient))
+
+    def ck_density_regularization(self, inner, contact=None, free_surface=True):
+        self.check(self.lib.sphb200_ck_density_regularization(inner.h, contact.h if contact else None, int(free_surface)))
+
+    def ck_linear_correction_matrix(self, inner, contact=None, alpha=0.0):
+        self.check(self.lib.sphb200_ck_linear_correction_matrix(inner.h, contact.h if contact else None, alpha))
+
+    def ck_free_surface_indication(self, inner, contact=None):
+        self.check(self.lib.sphb200_ck_free_surface_indication(inner.h, contact.h if contact else None))
 
     def total_kinetic_energy(self, body):
         out = C.c_double()
@@ -378,10 +399,17 @@ class Body:
 
 
 class Relation:
-    def __init__(self, system, body, targets):
+    def __init__(self, system, body, targets, builder=None, part_ids=None):
         self.sys, self.lib, self.body, self.targets = system, system.lib, body, targets
         h = C.c_void_p()
-        if targets is None:
+        ids = np.ascontiguousarray(part_ids if part_ids is not None else [], dtype=np.int64)
+        idp = ids.ctypes.data_as(C.POINTER(C.c_int64)) if ids.size else None
+        if builder == "self":
+            system.check(self.lib.sphb200_relation_self_contact_create(body.h, idp, ids.size, C.byref(h)))
+        elif builder == "surface":
+            arr = (C.c_void_p * len(targets))(*[t.h for t in targets])
+            system.check(self.lib.sphb200_relation_surface_contact_create(body.h, arr, len(targets), idp, ids.size, C.byref(h)))
+        elif targets is None:
             system.check(self.lib.sphb200_relation_inner_create(body.h, C.byref(h)))
         else:
             arr = (C.c_void_p * len(targets))(*[t.h for t in targets])

@@ -122,6 +122,90 @@ def test_neighbor_sets_inner_and_contact(pk, gpu, oracle, ndim, dp, real_bytes, 
         assert counts.max() == (20 if ndim == 2 else 80)  # interior lattice KAT, SURVEY §8c
 
 
+@pytest.mark.parametrize("ndim,dp,real_bytes", [(3, 0.05, 8), (2, 0.025, 8), (3, 0.05, 4)])
+def test_ck_flavour_dynamics(pk, gpu, oracle, ndim, dp, real_bytes):
+    """row f3: CompressionSummation + DensityRegularization<FreeSurface>, LinearCorrectionMatrix(alpha = 0.5) with the wall's
+    contact part, FreeSurfaceIndicationCK (two calls: the second sees PreviousSurfaceIndicator) - with the CK tabulated kernel,
+    on the jittered dam break against the oracle's statement-by-statement twins (oracle/oracle_ck.hpp)"""
+    g, o = both(pk, gpu, oracle, pk.cases.DamBreak, ndim=ndim, dp=dp, real_bytes=real_bytes)
+    out = {}
+    for name, c in (("gpu", g), ("oracle", o)):
+        jitter(c.water, 0.25)
+        c.water.update_cell_list()
+        c.update_configuration()
+        S = c.sys
+        S.ck_density_regularization(c.inner, c.wall_contact, True)
+        S.ck_linear_correction_matrix(c.inner, c.wall_contact, 0.5)
+        S.ck_free_surface_indication(c.inner, c.wall_contact)
+        first = field(c.water, "Indicator")
+        S.ck_free_surface_indication(c.inner, c.wall_contact)
+        out[name] = {nm: field(c.water, nm) for nm in ("CompressionSummation", "Compression", "Density", "LinearCorrectionMatrix",
+                                                       "PositionDivergence", "Indicator", "PreviousSurfaceIndicator")}
+        out[name]["Indicator1"] = first
+        S.ck_density_regularization(c.inner, None, False)        # Internal regularisation, inner only
+        out[name]["DensityInternal"] = field(c.water, "Density")
+    tol = FP_TOL[real_bytes]
+    for nm in ("CompressionSummation", "Compression", "Density", "DensityInternal", "LinearCorrectionMatrix", "PositionDivergence"):
+        assert rel_l2(out["gpu"][nm], out["oracle"][nm]) < tol, nm
+    for nm in ("Indicator", "Indicator1", "PreviousSurfaceIndicator"):
+        diff = np.count_nonzero(out["gpu"][nm] != out["oracle"][nm])
+        assert diff <= (0 if real_bytes == 8 else 3), (nm, diff)   # a threshold decision: exact in fp64
+    ind = out["gpu"]["Indicator"]
+    assert 0.05 * len(ind) < ind.sum() < 0.6 * len(ind)            # a surface layer, not everything
+    assert out["gpu"]["Compression"].min() >= 1.0 and out["gpu"]["DensityInternal"].min() < 1.0
+
+
+@pytest.mark.parametrize("real_bytes", [8, 4])
+def test_solid_contact_neighbor_builders(pk, gpu, oracle, real_bytes):
+    """row f4: NeighborBuilderSelfContact (neighborhood.cpp:123-142: r < rc and r0 > rc on InitialPosition, over a body
+    part by particle) and NeighborBuilderSurfaceContact (:162-168: kernel of the averaged smoothing length) on the same
+    cell lists: neighbour sets exactly equal to the oracle's, a folded sheet and two blocks of different resolution"""
+    dtype = np.float64 if real_bytes == 8 else np.float32
+    dp = 0.1
+    sets = {}
+    for name, be in (("gpu", gpu), ("oracle", oracle)):
+        s = be.SPHSystem(3, [-1, -1, -1], [5, 3, 3], dp, real_bytes=real_bytes)
+        # a sheet (2 layers) folded back onto itself: particles far apart initially come within the cut-off
+        u, v, w = np.meshgrid(np.arange(40), np.arange(12), np.arange(2), indexing="ij")
+        x0 = np.stack([u.ravel() * dp, v.ravel() * dp, w.ravel() * dp], 1).astype(dtype)
+        x = x0.copy()
+        fold = x0[:, 0] > 2.0
+        x[fold, 0] = 4.0 - x0[fold, 0]
+        x[fold, 2] = x0[fold, 2] + 0.23
+        sheet = s.add_body("Sheet", len(x), dp, h_ratio=1.15)
+        sheet.set("Position", x)
+        sheet.set("InitialPosition", x0)
+        sheet.set("VolumetricMeasure", np.full(len(x), dp ** 3, dtype))
+        part = np.nonzero(x0[:, 1] < 0.85)[0]           # the "surface layer": a body part by particle
+        sheet.update_cell_list()
+        rel = s.self_contact(sheet, part)
+        rel.update()
+        sets["self", name] = pair_set(rel)
+        counts, _ = rel.neighbors()
+        oid, _ = sheet.ids()
+        assert counts[~np.isin(oid, part)].sum() == 0     # particles outside the part keep empty neighbourhoods
+        # a coarser block under the sheet: surface contact with the averaged kernel
+        a, b, c = np.meshgrid(np.arange(12), np.arange(8), np.arange(3), indexing="ij")
+        xb = np.stack([a.ravel() * 0.16 + 0.03, b.ravel() * 0.16, c.ravel() * 0.16 - 0.55], 1).astype(dtype)
+        block = s.add_body("Block", len(xb), 0.16, h_ratio=1.15)
+        block.set("Position", xb)
+        block.set("VolumetricMeasure", np.full(len(xb), 0.16 ** 3, dtype))
+        block.update_cell_list()
+        for tag, src, tgt in (("surf_fine", sheet, block), ("surf_coarse", block, sheet)):
+            r2 = s.surface_contact(src, [tgt])
+            r2.update()
+            sets[tag, name] = pair_set(r2, 0, tgt)
+            plain = s.contact(src, [tgt])
+            plain.update()
+            sets[tag + "_plain", name] = pair_set(plain, 0, tgt)
+    for key in ("self", "surf_fine", "surf_coarse"):
+        assert len(sets[key, "gpu"]) > 100 and np.array_equal(sets[key, "gpu"], sets[key, "oracle"]), key
+    # the averaged kernel reaches less far than the larger one the plain contact builder picks
+    assert len(sets["surf_fine", "gpu"]) < len(sets["surf_fine_plain", "gpu"])
+    # self contact: no pair that was within the cut-off initially
+    assert len(sets["self", "gpu"]) < 0.2 * 80 * 960
+
+
 def test_search_prefilter_is_exact(pk, gpu):
     """relation.cu: the fp32 pre-filter of the fp64 search may only decide what the exact test
     (neighborhood.cpp:85-98: d.d < rc^2 on the fp64 positions) decides the same way.  Random particles far from
