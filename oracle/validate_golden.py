@@ -77,7 +77,7 @@ def compare(quantity, ours):
     else:
         dev = np.maximum(dev, 0.0)
         scale = np.abs(stack).max(axis=(0, 2))[:, None]
-    rel = dev / scale
+    rel = dev / np.maximum(scale, 1e-300)
     return {"dtw": dtw, "dtw_limit": [1.01 * x for x in limits], "dtw_ok": bool(all(d <= 1.01 * x for d, x in zip(dtw, limits))),
             "max_rel_dev": float(rel.max()), "first_sample_over_1pct": int(np.argmax(rel.max(0) > 0.01)) if (rel > 0.01).any() else None,
             "snapshots": [int(ours.shape[1]), int(stack.shape[2])]}
