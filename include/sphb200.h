@@ -278,19 +278,29 @@ sphb200_status sphb200_body_keep_range(sphb200_body *b, int64_t begin, int64_t e
 /* index of the first particle (cell-sorted order) whose cell page along axis 0 is >= page; needs a valid
  * cell list.  page <= 0 gives 0, page >= number of pages gives n */
 sphb200_status sphb200_body_page_begin(sphb200_body *b, int page, int64_t *out);
+/* out[p] = page_begin(p) for p = 0..n_pages (n_pages + 1 values; out may be NULL to query n_pages): the per-page
+ * particle counts a re-cut of the slabs needs, in one strided device-to-host copy */
+sphb200_status sphb200_body_page_offsets(sphb200_body *b, int64_t *out, int64_t *n_pages);
 /* the packed gather records of the acoustic sub-step (Rec8 = 8 Reals per particle {x,y,z,p|Vol,vx,vy,vz},
  * which = 0: rec_a written by the 1st-half initialization, 1: rec_b written by the 1st-half update).  A
  * slab run overwrites the records of its halo copies with the owner's between the stages. */
 sphb200_status sphb200_body_record_ptr(sphb200_body *b, int which, void **out);
 /* Re-decomposition of a slab after an advection step, without a cell-list update of the old arrangement:
- * slab_select classifies the rows by the axis-0 cell page of their CURRENT position (halo copies are dropped; owned
- * rows stay if their page is still owned, go to the left slab if page <= page_lo, to the right one if page >=
- * page_hi - 1 - as migrants or as that slab's fresh halo) and returns counts3 = {stay, to left, to right};
+ * slab_select classifies the rows by the axis-0 cell page of their CURRENT position (old halo copies are dropped; owned
+ * rows stay if their page is in [page_lo - 1, page_hi + 1) - as owned rows or as this slab's own fresh halo copy of a
+ * migrant - go to the left slab if page <= page_lo, to the right one if page >= page_hi - 1 - as migrants or as that
+ * slab's fresh halo) and returns counts3 = {stay, to left, to right}.  The pages are the CURRENT owned pages: call
+ * sphb200_slab_recut first to move a cut (load re-balancing; a cut may move by less than the width of the
+ * slabs either side, so that every row a slab needs is owned by itself or a direct neighbour);
  * slab_pack gathers the listed variables of the rows going to `side` (1 left, 2 right) into a row-major device
  * buffer [count x sum(width)]; slab_rebuild makes the body {staying rows, rows received from the left, from the
  * right} (every variable compacted in one pass, listed variables filled from the received buffers, the others
  * zero), resets the ids and invalidates the cell list: ONE cell_list_update then sorts the new arrangement. */
 sphb200_status sphb200_slab_select(sphb200_body *b, int has_left, int has_right, int64_t *counts3);
+/* move the cuts of this slab: the owned pages become [page_lo, page_hi) for the next slab_select / cell_list_update,
+ * the owned RANGE stays that of the current arrangement until then (unlike body_set_owned_pages, which re-derives it
+ * at once) */
+sphb200_status sphb200_slab_recut(sphb200_body *b, int page_lo, int page_hi);
 sphb200_status sphb200_slab_pack(sphb200_body *b, int side, const char *const *names, int n_names, void *out);
 sphb200_status sphb200_slab_rebuild(sphb200_body *b, const char *const *names, int n_names, const void *from_left, int64_t n_left,
                                     const void *from_right, int64_t n_right);

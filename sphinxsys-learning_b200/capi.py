@@ -75,6 +75,7 @@ SIGNATURES = {
     "sphb200_substep_ctl": (_i, [_vp, _d, _i, _i]),
     "sphb200_reduce_slot_ptr": (_i, [_vp, _i, _vpp]),
     "sphb200_slab_select": (_i, [_vp, _i, _i, _i64p]),
+    "sphb200_slab_recut": (_i, [_vp, _i, _i]),
     "sphb200_slab_pack": (_i, [_vp, _i, C.POINTER(C.c_char_p), _i, _vp]),
     "sphb200_slab_rebuild": (_i, [_vp, C.POINTER(C.c_char_p), _i, _vp, _i64, _vp, _i64]),
     "sphb200_rows_gather": (_i, [_vp, _vp, _i, _vp, _i64, _vp]),
@@ -103,6 +104,7 @@ SIGNATURES = {
     "sphb200_ids_device_ptr": (_i, [_vp, _vpp, _vpp]),
     "sphb200_body_keep_range": (_i, [_vp, _i64, _i64]),
     "sphb200_body_page_begin": (_i, [_vp, _i, _i64p]),
+    "sphb200_body_page_offsets": (_i, [_vp, _i64p, _i64p]),
     "sphb200_body_record_ptr": (_i, [_vp, _i, _vpp]),
     "sphb200_integration_1st_half_init": (_i, [_vp, _d]),
     "sphb200_integration_1st_half_interact": (_i, [_vp, _vp, _i, _d]),

@@ -36,7 +36,10 @@ __global__ void k_slab_flags(int64_t n, int64_t ob, int64_t oe, const R *__restr
         int c[D];
         mesh.cellIndex(pos + i * D, c);
         const int px = c[0];
-        k = (px >= p_lo && px < p_hi) ? 1u : 0u;
+        // kept: my pages AND the two halo pages.  A row that leaves through a cut is sent to that neighbour as a migrant
+        // and stays here as a halo copy (the neighbour only sends rows IT owned, so nothing arrives twice); with the
+        // owned pages changed before this call (re-cut) the same rule moves whole pages.
+        k = (px >= p_lo - 1 && px < p_hi + 1) ? 1u : 0u;
         l = (has_left && px <= p_lo) ? 1u : 0u;
         r = (has_right && px >= p_hi - 1) ? 1u : 0u;
     }
@@ -345,6 +348,36 @@ sphb200_status sphb200_body_keep_range(sphb200_body *b, int64_t begin, int64_t e
     return sphb200_body_resize(b, keep);
 }
 
+sphb200_status sphb200_body_page_offsets(sphb200_body *b, int64_t *out, int64_t *n_pages)
+{
+    if (!b || !n_pages)
+        return SPHB200_ERR_INVALID;
+    sphb200_ctx *ctx = b->ctx;
+    cudaSetDevice(ctx->device);
+    double info[12];
+    SPHB_TRY(sphb200_body_info(b, info));
+    int64_t per_page = 1;
+    for (int d = 1; d < ctx->ndim; ++d)
+        per_page *= int64_t(info[8 + d]);
+    const int64_t pages = int64_t(info[8]);
+    *n_pages = pages;
+    if (!out)
+        return SPHB200_OK;
+    if (!b->cell_list_valid)
+        return ctx->fail(SPHB200_ERR_INVALID, "body_page_offsets: cell_list_update has not been called");
+    // one strided copy: element p of the result = cell_offset[p * per_page]
+    std::vector<u32> host(size_t(pages) + 1, 0u);
+    if (b->n > 0)
+    {
+        SPHB_CUDA(ctx, cudaMemcpy2DAsync(host.data(), 4, b->cell_offset.p, size_t(per_page) * 4, 4, size_t(pages) + 1,
+                                         cudaMemcpyDeviceToHost, ctx->stream));
+        SPHB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    for (int64_t p = 0; p <= pages; ++p)
+        out[p] = int64_t(host[size_t(p)]);
+    return SPHB200_OK;
+}
+
 sphb200_status sphb200_body_page_begin(sphb200_body *b, int page, int64_t *out)
 {
     if (!b || !out)
@@ -398,6 +431,19 @@ sphb200_status sphb200_body_set_owned_pages(sphb200_body *b, int page_lo, int pa
     b->page_hi = page_lo < 0 ? -1 : page_hi;
     if (b->cell_list_valid)
         return updateOwnedRange(b);
+    return SPHB200_OK;
+}
+
+sphb200_status sphb200_slab_recut(sphb200_body *b, int page_lo, int page_hi)
+{
+    if (!b || page_lo < 0 || page_hi < page_lo)
+        return SPHB200_ERR_INVALID;
+    if (b->page_lo < 0)
+        return b->ctx->fail(SPHB200_ERR_INVALID, "slab_recut: body has no owned pages (body_set_owned_pages)");
+    // the owned RANGE stays that of the current arrangement (slab_select classifies exactly those rows, by the new
+    // pages); the next cell_list_update translates the new pages into the new range
+    b->page_lo = page_lo;
+    b->page_hi = page_hi;
     return SPHB200_OK;
 }
 

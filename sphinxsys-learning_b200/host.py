@@ -369,6 +369,9 @@ class Body:
         self.sys.check(self.lib.sphb200_slab_select(self.h, int(has_left), int(has_right), out))
         return int(out[0]), int(out[1]), int(out[2])
 
+    def slab_recut(self, lo, hi):
+        self.sys.check(self.lib.sphb200_slab_recut(self.h, int(lo), int(hi)))
+
     def slab_pack(self, side, names, out_ptr):
         arr = (C.c_char_p * len(names))(*[n.encode() for n in names])
         self.sys.check(self.lib.sphb200_slab_pack(self.h, int(side), arr, len(names), C.c_void_p(out_ptr)))
@@ -386,6 +389,14 @@ class Body:
         out = C.c_int64()
         self.sys.check(self.lib.sphb200_body_page_begin(self.h, int(page), C.byref(out)))
         return out.value
+
+    def page_offsets(self):
+        """page_begin(p) for every page boundary p = 0..pages (sphb200_body_page_offsets)"""
+        n = C.c_int64()
+        self.sys.check(self.lib.sphb200_body_page_offsets(self.h, None, C.byref(n)))
+        out = np.zeros(n.value + 1, dtype=np.int64)
+        self.sys.check(self.lib.sphb200_body_page_offsets(self.h, out.ctypes.data_as(C.POINTER(C.c_int64)), C.byref(n)))
+        return out
 
     def record_ptr(self, which):
         p = C.c_void_p()

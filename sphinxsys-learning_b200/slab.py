@@ -64,6 +64,26 @@ def page_cuts(fluid_per_page, n_slabs):
     return cuts
 
 
+def recut(fluid_per_page, old_cuts):
+    """new page cuts for the current fluid distribution, every interior cut moved by at most half the width of the
+    narrower slab next to it minus one page: then each page a slab needs (its own and one halo page either side) is
+    owned, before the move, by the slab itself or a direct neighbour, and one neighbour exchange re-decomposes the run"""
+    n = len(old_cuts) - 1
+    want = page_cuts(fluid_per_page, n)
+    new = list(old_cuts)
+    for r in range(1, n):
+        room = max(min(old_cuts[r] - old_cuts[r - 1], old_cuts[r + 1] - old_cuts[r]) // 2 - 1, 0)
+        new[r] = min(max(want[r], old_cuts[r] - room), old_cuts[r] + room)
+    return new
+
+
+def imbalance(fluid_per_page, cuts):
+    """max over slabs of owned fluid / mean - 1"""
+    c = np.concatenate([[0], np.cumsum(np.asarray(fluid_per_page, dtype=np.int64))])
+    owned = np.array([c[b] - c[a] for a, b in zip(cuts, cuts[1:])], dtype=np.float64)
+    return float(owned.max() / max(owned.mean(), 1.0) - 1.0)
+
+
 def match_by_gid(send_gid, recv_gid):
     """orders that make sender rows and receiver slots line up: both sides sort by global id"""
     return np.argsort(send_gid, kind="stable"), np.argsort(recv_gid, kind="stable")
@@ -94,6 +114,10 @@ class LocalComm:
     def allreduce(self, values, op):
         v = min(values) if op == "min" else (max(values) if op == "max" else sum(values))
         return v
+
+    def allreduce_sum_array(self, arrays):
+        """arrays: one host int64 array per local slab; returns their element-wise sum over all slabs"""
+        return np.sum(np.stack(arrays), axis=0)
 
     def allreduce_max_device(self, slots):
         """slots: one int64 device tensor per local slab (bit pattern of a non-negative double): all get the maximum"""
@@ -170,6 +194,11 @@ class DistComm:
         dist.all_reduce(t, op={"min": dist.ReduceOp.MIN, "max": dist.ReduceOp.MAX, "sum": dist.ReduceOp.SUM}[op])
         return float(t.item())
 
+    def allreduce_sum_array(self, arrays):
+        t = torch.as_tensor(np.asarray(arrays[0], dtype=np.int64), device=self.device)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return t.cpu().numpy()
+
     def allreduce_max_device(self, slots):
         dist.all_reduce(slots[0], op=dist.ReduceOp.MAX)  # stays on the device: no host synchronisation
 
@@ -186,6 +215,7 @@ def _exchange_fixed(comm, sends, recv_rows):
 # ------------------------------------------------------------------------------------------------
 # the decomposed 3-D dam break
 # ------------------------------------------------------------------------------------------------
+WALL_VARS = ["Position", "VolumetricMeasure", "Mass", "NormalDirection", "Velocity", "Acceleration"]
 MIGRATE_VARS = ["Position", "VolumetricMeasure", "Mass", "Density", "Pressure", "DensityChangeRate", "Velocity", "Force",
                 "ForcePrior", "PreviousGravityForce", "GlobalID"]
 
@@ -198,13 +228,17 @@ class _Part:
 class SlabDamBreak:
     """tests/3d_examples/test_3d_dambreak/dambreak.cpp:159-195 over n_slabs slabs; same loop as cases.DamBreak"""
 
-    def __init__(self, backend, comm, dp=0.05, real_bytes=8, device=0, stream=None, ndim=3, device_loop=True, fast_reconfigure=True):
-        """device_loop: dt / relaxation time / exit test of the sub-step loop on the device (False: one host round trip
+    def __init__(self, backend, comm, dp=0.05, real_bytes=8, device=0, stream=None, ndim=3, device_loop=True, fast_reconfigure=True,
+                 recut_interval=20, recut_threshold=0.05):
+        """recut_interval / recut_threshold: every recut_interval advection steps the owned fluid per page is summed over
+        the slabs and, when the fullest slab holds more than (1 + threshold) x the mean, the cuts move (SURVEY 8e; 0 = never);
+        device_loop: dt / relaxation time / exit test of the sub-step loop on the device (False: one host round trip
         per sub-step, the round-1 path); fast_reconfigure: sphb200_slab_select/pack/rebuild and one cell-list update
         per advection step (False: keep_range + two cell-list updates + torch.cat, the round-1 path)"""
         assert torch is not None
         self.comm, self.dp, self.ndim, self.real_bytes = comm, dp, ndim, real_bytes
         self.device_loop, self.fast_reconfigure, self._guess = device_loop, fast_reconfigure, 5
+        self.recut_interval, self.recut_threshold, self.n_recuts = (recut_interval if fast_reconfigure else 0), recut_threshold, 0
         self.device = torch.device("cuda", device)
         self.np_real = np.float64 if real_bytes == 8 else np.float32
         self.np_int = np.int64 if real_bytes == 8 else np.int32
@@ -251,6 +285,7 @@ class SlabDamBreak:
                 a, b = body.page_begin(P.p_lo - 1), body.page_begin(P.p_hi + 1)
                 body.keep_range(a, b)
             w.set_owned_pages(P.p_lo, P.p_hi)
+            s.set_owned_pages(P.p_lo, P.p_hi)   # the wall is only ever a target; its owned pages serve the re-cut
             w.update_cell_list()
             s.update_cell_list()
             c.update_configuration(observer=False)
@@ -373,32 +408,71 @@ class SlabDamBreak:
         self.reconfigure()
         return Dt, k
 
-    def reconfigure(self):
-        """migration + fresh halo in one exchange, then ONE sort, relations and halo maps"""
-        if not self.fast_reconfigure:
-            return self.reconfigure_two_sorts()
+    def fluid_per_page(self):
+        """owned fluid particles per cell page, summed over the slabs (every rank gets the same array)"""
+        local = []
+        for P in self.parts:
+            off = P.case.water.page_offsets()
+            cnt = np.diff(off)
+            cnt[:P.p_lo] = 0
+            cnt[P.p_hi:] = 0
+            local.append(cnt)
+        return self.comm.allreduce_sum_array(local)
+
+    def plan_recut(self, force=False):
+        """the new cuts, or None when the slabs are balanced (needs the cell lists of the current arrangement: call it
+        before the particles move, i.e. right after a reconfigure; the cuts take effect in the next one)"""
+        per_page = self.fluid_per_page()
+        if not force and imbalance(per_page, self.cuts) <= self.recut_threshold:
+            return None
+        new = recut(per_page, self.cuts)
+        return None if new == list(self.cuts) else new
+
+    def _move(self, body_of, names, t_real):
+        """select -> pack -> neighbour exchange -> rebuild for one body of every local slab"""
         sends = []
         for P in self.parts:
-            w = P.case.water
-            _, n_l, n_r = w.slab_select(P.has_left, P.has_right)
-            width = sum(w.width(nm) for nm in MIGRATE_VARS)
-            t_real = torch.float64 if self.real_bytes == 8 else torch.float32
+            b = body_of(P)
+            _, n_l, n_r = b.slab_select(P.has_left, P.has_right)
+            width = sum(b.width(nm) for nm in names)
             bl = torch.empty((n_l, width), dtype=t_real, device=self.device)
             br = torch.empty((n_r, width), dtype=t_real, device=self.device)
             if n_l:
-                w.slab_pack(1, MIGRATE_VARS, bl.data_ptr())
+                b.slab_pack(1, names, bl.data_ptr())
             if n_r:
-                w.slab_pack(2, MIGRATE_VARS, br.data_ptr())
+                b.slab_pack(2, names, br.data_ptr())
             sends.append((bl if P.has_left else None, br if P.has_right else None))
         recvs = self.comm.exchange(sends)
         for P, (fl, fr) in zip(self.parts, recvs):
-            w = P.case.water
+            b = body_of(P)
             nl = fl.shape[0] if fl is not None else 0
             nr = fr.shape[0] if fr is not None else 0
-            w.slab_rebuild(MIGRATE_VARS, fl.data_ptr() if nl else 0, nl, fr.data_ptr() if nr else 0, nr)
-            w.update_cell_list()
+            b.slab_rebuild(names, fl.data_ptr() if nl else 0, nl, fr.data_ptr() if nr else 0, nr)
+
+    def reconfigure(self):
+        """migration + fresh halo in one exchange (and, when a re-cut is pending, whole pages of fluid and wall with
+        it), then ONE sort, relations and halo maps"""
+        if not self.fast_reconfigure:
+            return self.reconfigure_two_sorts()
+        t_real = torch.float64 if self.real_bytes == 8 else torch.float32
+        new_cuts, self._pending_cuts = getattr(self, "_pending_cuts", None), None
+        if new_cuts is not None:
+            self.cuts = list(new_cuts)
+            for P in self.parts:
+                P.p_lo, P.p_hi = self.cuts[P.rank], self.cuts[P.rank + 1]
+                P.case.water.slab_recut(P.p_lo, P.p_hi)
+                P.case.wall.slab_recut(P.p_lo, P.p_hi)
+            self._move(lambda P: P.case.wall, WALL_VARS, t_real)
+            for P in self.parts:
+                P.case.wall.update_cell_list()
+            self.n_recuts += 1
+        self._move(lambda P: P.case.water, MIGRATE_VARS, t_real)
+        for P in self.parts:
+            P.case.water.update_cell_list()
             P.case.update_configuration(observer=False)
         self._halo_maps()
+        if self.recut_interval and self.n_advection % self.recut_interval == 0:
+            self._pending_cuts = self.plan_recut()
 
     def reconfigure_two_sorts(self):
         """the round-1 path (kept for A/B timing and as a cross-check of the fast one)"""

@@ -34,6 +34,29 @@ def test_page_cuts_balance_and_cover(slab):
     assert cuts == sorted(cuts) and len(set(cuts)) == 5
 
 
+def test_recut_moves_cuts_towards_balance_within_the_neighbour_bound(slab):
+    # a column of fluid that has slumped to the right: the old cuts leave slab 0 over-full
+    per_page = np.array([0, 0] + [9] * 12 + [5] * 12 + [2] * 12 + [0] * 4)
+    old = slab.page_cuts([0, 0] + [9] * 12 + [0] * 28, 3)
+    assert slab.imbalance(per_page, old) > 0.5
+    cuts = list(old)
+    for _ in range(12):
+        new = slab.recut(per_page, cuts)
+        assert new[0] == 0 and new[-1] == len(per_page) and all(b > a for a, b in zip(new, new[1:]))
+        for r in range(1, 3):
+            # a cut never moves past the middle of a neighbouring slab: one neighbour exchange suffices
+            room = max(min(cuts[r] - cuts[r - 1], cuts[r + 1] - cuts[r]) // 2 - 1, 0)
+            assert abs(new[r] - cuts[r]) <= room
+            assert new[r] >= cuts[r - 1] + 2 or new[r] == cuts[r]
+            assert new[r] <= cuts[r + 1] - 2 or new[r] == cuts[r]
+        if new == cuts:
+            break
+        assert slab.imbalance(per_page, new) <= slab.imbalance(per_page, cuts) + 1e-12
+        cuts = new
+    assert cuts == slab.page_cuts(per_page, 3)       # bounded moves converge to the balanced cuts
+    assert slab.imbalance(per_page, cuts) < 0.06
+
+
 def test_match_by_gid(slab):
     rng = np.random.default_rng(3)
     gid = rng.permutation(1000)[:200]
@@ -66,6 +89,9 @@ else:
 other = fr if r == 0 else fl
 assert other.shape == (2, 8) and float(other[0, 0]) == float(1 - r)
 assert comm.allreduce([float(r + 1)], "min") == 1.0 and comm.allreduce([float(r + 1)], "sum") == 3.0
+import numpy as np
+tot = comm.allreduce_sum_array([np.arange(5, dtype=np.int64) * (r + 1)])     # per-page fluid counts of a re-cut
+assert tot.dtype == np.int64 and tot.tolist() == [0, 3, 6, 9, 12]
 dist.destroy_process_group()
 print("ok", r)
 '''
@@ -123,3 +149,59 @@ def test_slabs_equal_single_gpu(pk, gpu, slab, n_slabs, real_bytes, pair_kernel,
         assert err < tol, (name, err)
     e1, en = one.mechanical_energy(), many.mechanical_energy()
     assert abs(e1 - en) <= 1e-9 * abs(e1) if real_bytes == 8 else abs(e1 - en) <= 1e-4 * abs(e1)
+
+
+def _compare_owned_with_single(one, many, dp, tol):
+    pos_names = ("Position", "Velocity", "Density", "Pressure", "DensityChangeRate", "Force")
+    oid, _ = one.water.ids()
+    worst = 0.0
+    for name in pos_names:
+        ref = one.water.get(name)
+        g, v = many.owned(name)
+        assert len(g) == one.water.n and len(np.unique(g)) == len(g)     # every particle owned exactly once
+        order, o2 = np.argsort(one._gid_by_oid[oid]), np.argsort(g)
+        assert np.array_equal(one._gid_by_oid[oid][order], g[o2])
+        a, b = v[o2].astype(np.float64).reshape(len(g), -1), ref[order].astype(np.float64).reshape(len(g), -1)
+        err = np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
+        worst = max(worst, err)
+        assert err < tol, (name, err)
+    return worst
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_slabs,recut_interval", [(3, 0), (3, 5), (4, 3)])
+def test_migration_and_recut_over_a_collapsing_column(pk, gpu, slab, n_slabs, recut_interval):
+    """long enough for particles to cross the cuts (migrants must stay behind as the sender's halo copies) and, with
+    recut_interval > 0, for the cuts themselves to follow the front (whole pages of fluid and wall change slabs):
+    the decomposed run still equals the undecomposed one, halo sets included (checked through the sums)"""
+    dp, steps = 0.05, 140
+    one = pk.cases.DamBreak(gpu, ndim=3, dp=dp, real_bytes=8, with_observer=False)
+    many = slab.SlabDamBreak(gpu, slab.LocalComm(n_slabs), dp=dp, real_bytes=8, recut_interval=recut_interval, recut_threshold=0.0)
+    pos0 = one.water.get("Position").astype(np.float64)
+    oid0, _ = one.water.ids()
+    idx = np.rint((pos0 - many.sys_lo) / dp - 0.5).astype(np.int64)
+    gid_sorted = (idx[:, 0] * int(many.n_lat[1]) + idx[:, 1]) * int(many.n_lat[2]) + idx[:, 2]
+    one._gid_by_oid = np.empty_like(gid_sorted)
+    one._gid_by_oid[oid0] = gid_sorted
+    cuts0 = list(many.cuts)
+    owner0 = {}
+    for P in many.parts:
+        g = many._gid(P)[P.ob:P.oe].cpu().numpy()
+        owner0.update({int(k): P.rank for k in g})
+    for s in range(steps):
+        r1, rn = one.advection_step(), many.advection_step()
+        assert r1[1] == rn[1] and abs(r1[0] - rn[0]) <= 1e-12 * r1[0], (s, r1, rn)
+        assert sum(P.oe - P.ob for P in many.parts) == one.water.n
+    moved = 0
+    for P in many.parts:
+        g = many._gid(P)[P.ob:P.oe].cpu().numpy()
+        moved += sum(1 for k in g if owner0[int(k)] != P.rank)
+    assert moved > 50, moved                                 # particles did change slabs
+    if recut_interval:
+        assert many.n_recuts >= 1 and list(many.cuts) != cuts0, (many.n_recuts, many.cuts)
+        assert slab.imbalance(many.fluid_per_page(), many.cuts) < slab.imbalance(many.fluid_per_page(), cuts0)
+    else:
+        assert list(many.cuts) == cuts0
+    worst = _compare_owned_with_single(one, many, dp, 1e-7)
+    e1, en = one.mechanical_energy(), many.mechanical_energy()
+    assert abs(e1 - en) <= 1e-9 * abs(e1), (e1, en, worst)
