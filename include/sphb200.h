@@ -308,6 +308,25 @@ sphb200_status sphb200_slab_rebuild(sphb200_body *b, const char *const *names, i
  * all device pointers, on the context's stream */
 sphb200_status sphb200_rows_gather(sphb200_ctx *ctx, const void *src, int row_bytes, const int64_t *idx, int64_t n, void *dst);
 sphb200_status sphb200_rows_scatter(sphb200_ctx *ctx, void *dst, int row_bytes, const int64_t *idx, int64_t n, const void *src);
+/* Halo records over NVLink peer memory (csrc/peer.cu): the pack kernel stores the rows straight into a landing buffer in
+ * the neighbour GPU's memory and publishes `epoch` (a counter that grows with every refresh, the same on both sides) in the
+ * neighbour's flag word; the neighbour waits for that epoch on ITS stream (bounded spin on the device, no host) and unpacks.
+ *   peer_alloc / peer_free     landing buffers and flag words (zero-filled, exportable allocations)
+ *   peer_export / peer_open    64-byte handle of an allocation / the mapping of another process's allocation on this device
+ *                              (cudaIpcGetMemHandle / cudaIpcOpenMemHandle; inside one process pass the pointer itself)
+ *   rows_push                  peer_landing[r] = src[idx[r]] for n rows, then *peer_flag = epoch (release, system scope)
+ *   rows_wait_scatter          wait until *flag >= epoch, then dst[idx[r]] = landing[r]
+ *   peer_timeouts              number of waits that gave up after ~5 s (a dead neighbour must not hang the device) */
+sphb200_status sphb200_peer_alloc(sphb200_ctx *ctx, int64_t bytes, void **out);
+sphb200_status sphb200_peer_free(sphb200_ctx *ctx, void *p);
+sphb200_status sphb200_peer_export(sphb200_ctx *ctx, const void *p, unsigned char handle64[64]);
+sphb200_status sphb200_peer_open(sphb200_ctx *ctx, const unsigned char handle64[64], void **out);
+sphb200_status sphb200_peer_close(sphb200_ctx *ctx, void *p);
+sphb200_status sphb200_rows_push(sphb200_ctx *ctx, const void *src, int row_bytes, const int64_t *idx, int64_t n, void *peer_landing,
+                                 void *peer_flag, uint64_t epoch);
+sphb200_status sphb200_rows_wait_scatter(sphb200_ctx *ctx, void *dst, int row_bytes, const int64_t *idx, int64_t n, const void *landing,
+                                         const void *flag, uint64_t epoch);
+sphb200_status sphb200_peer_timeouts(sphb200_ctx *ctx, int64_t *out);
 /* Dynamics1Level<Integration1stHalf...>::exec split into its two particle loops
  * (particle_dynamics/dynamics_algorithms.h:336-352): initialization (fluid_integration.hpp:50-55), then
  * interaction + update (:58-113), so that a slab run can refresh the halo pressures in between */

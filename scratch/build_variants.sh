@@ -8,7 +8,7 @@ for spec in "$@"; do
   name="${spec%%:*}"; extra="${spec#*:}"
   (
     mkdir -p /tmp/t/$name
-    for f in context cell_list relation fluid solid slab ck; do nvcc $FLAGS $extra -c $f.cu -o /tmp/t/$name/$f.o & done; wait
+    for f in context cell_list relation fluid solid slab ck peer; do nvcc $FLAGS $extra -c $f.cu -o /tmp/t/$name/$f.o & done; wait
     nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../../scratch/variants/$name.so /tmp/t/$name/*.o -lcudart
   ) &
 done

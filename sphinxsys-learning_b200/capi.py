@@ -80,6 +80,14 @@ SIGNATURES = {
     "sphb200_slab_rebuild": (_i, [_vp, C.POINTER(C.c_char_p), _i, _vp, _i64, _vp, _i64]),
     "sphb200_rows_gather": (_i, [_vp, _vp, _i, _vp, _i64, _vp]),
     "sphb200_rows_scatter": (_i, [_vp, _vp, _i, _vp, _i64, _vp]),
+    "sphb200_peer_alloc": (_i, [_vp, _i64, _vpp]),
+    "sphb200_peer_free": (_i, [_vp, _vp]),
+    "sphb200_peer_export": (_i, [_vp, _vp, C.c_char_p]),
+    "sphb200_peer_open": (_i, [_vp, C.c_char_p, _vpp]),
+    "sphb200_peer_close": (_i, [_vp, _vp]),
+    "sphb200_rows_push": (_i, [_vp, _vp, _i, _vp, _i64, _vp, _vp, C.c_uint64]),
+    "sphb200_rows_wait_scatter": (_i, [_vp, _vp, _i, _vp, _i64, _vp, _vp, C.c_uint64]),
+    "sphb200_peer_timeouts": (_i, [_vp, _i64p]),
     "sphb200_gravity_force": (_i, [_vp, _dp]),
     "sphb200_viscous_force": (_i, [_vp, _vp]),
     "sphb200_transport_velocity_correction": (_i, [_vp, _d]),

@@ -237,6 +237,7 @@ void sphb200_ctx_destroy(sphb200_ctx *ctx)
     cudaStreamSynchronize(ctx->stream);
     if (ctx->copy_stream)
         cudaStreamSynchronize(ctx->copy_stream);
+    cudaFree(ctx->peer_words);
     for (auto *r : ctx->relations)
     {
         for (auto &l : r->lists)

@@ -242,6 +242,7 @@ struct sphb200_ctx
     cudaEvent_t fetch_ready = nullptr, fetch_done = nullptr;
     std::string error;
     int64_t launches = 0;
+    unsigned int *peer_words = nullptr; // peer.cu: [0] blocks-done counter of k_rows_push, [1] wait time-outs
     int pair_kernel = -2; // -2: process default (env SPHB200_TILE), -1 auto, 0 per-particle lists, 1 group-tiled
     std::vector<sphb200_body *> bodies;
     std::vector<sphb200_relation *> relations;

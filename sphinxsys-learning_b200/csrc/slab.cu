@@ -4,6 +4,7 @@
 // contiguous run of the cell-sorted particles this rank owns, and share the caller's stream.
 #include "internal.cuh"
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 using namespace sphb;
@@ -183,7 +184,51 @@ static sphb200_status slabRebuildT(sphb200_body *b, const std::vector<Var *> &va
     const int64_t n_keep = b->slab_count[0], n_new = n_keep + n_left + n_right;
     if (n_new >= (int64_t(1) << 31))
         return ctx->fail(SPHB200_ERR_INVALID, "slab_rebuild: too many particles");
-    for (auto &kv : b->vars)
+    // ---- in-place path: every owned row stays (the usual case: a row leaves only through the domain faces), so the
+    // kept rows are the contiguous range [ob, oe) and only the old halo copies either side of it go.  The received rows
+    // are written behind oe and the tail of the result is copied into the hole [0, ob): O(halo) bytes moved instead of
+    // one gather pass over every variable of the body (2.9 -> 0.3 ms per advection step at 20 M particles per slab).
+    // The next cell_list_update sorts the arrangement anyway, so the row order is free.
+    const int64_t ob = b->own_begin, oe = b->own_end, n_recv = n_left + n_right;
+    bool in_place = n_keep == oe - ob && n_keep > 0 && ob <= n_new;
+    if (const char *e = getenv("SPHB200_SLAB_INPLACE")) // 0: always the gather path (A/B timing, tests of both paths)
+        in_place = in_place && atoi(e) != 0;
+    if (in_place)
+        for (auto &kv : b->vars)
+            if (size_t(oe + n_recv) * size_t(kv.second->width) * sizeof(T) > kv.second->dev.bytes)
+                in_place = false;
+    if (in_place)
+    {
+        for (auto &kv : b->vars)
+        {
+            Var &v = *kv.second;
+            const size_t row = size_t(v.width) * sizeof(T);
+            int col = 0;
+            bool carried = false;
+            for (Var *m : vars)
+            {
+                if (m == &v)
+                {
+                    carried = true;
+                    if (n_left > 0)
+                        k_place_cols<T><<<gridFor(n_left * v.width, 256), 256, 0, st>>>(n_left, v.width, static_cast<const T *>(from_left), W, col,
+                                                                                    static_cast<T *>(v.dev.p), oe);
+                    if (n_right > 0)
+                        k_place_cols<T><<<gridFor(n_right * v.width, 256), 256, 0, st>>>(n_right, v.width, static_cast<const T *>(from_right), W, col,
+                                                                                     static_cast<T *>(v.dev.p), oe + n_left);
+                    SPHB_LAUNCH_CHECK(ctx);
+                    break;
+                }
+                col += m->width;
+            }
+            if (!carried && n_recv > 0)
+                SPHB_CUDA(ctx, cudaMemsetAsync(static_cast<char *>(v.dev.p) + size_t(oe) * row, 0, size_t(n_recv) * row, st));
+            if (ob > 0) // rows [n_new, n_new + ob) -> [0, ob); disjoint because ob <= n_new
+                SPHB_CUDA(ctx, cudaMemcpyAsync(v.dev.p, static_cast<char *>(v.dev.p) + size_t(n_new) * row, size_t(ob) * row, cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    else // generic: one gather pass per variable into the twin buffer
+        for (auto &kv : b->vars)
     {
         Var &v = *kv.second;
         const size_t row = size_t(v.width) * sizeof(T);

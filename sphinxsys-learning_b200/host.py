@@ -176,6 +176,41 @@ class SPHSystem:
     def rows_scatter(self, dst_ptr, row_bytes, idx_ptr, n, src_ptr):
         self.check(self.lib.sphb200_rows_scatter(self.h, C.c_void_p(dst_ptr), int(row_bytes), C.c_void_p(idx_ptr), int(n), C.c_void_p(src_ptr)))
 
+    # ---- halo records over peer memory (csrc/peer.cu)
+    def peer_alloc(self, nbytes):
+        p = C.c_void_p()
+        self.check(self.lib.sphb200_peer_alloc(self.h, int(nbytes), C.byref(p)))
+        return p.value
+
+    def peer_free(self, ptr):
+        self.check(self.lib.sphb200_peer_free(self.h, C.c_void_p(ptr)))
+
+    def peer_export(self, ptr):
+        buf = C.create_string_buffer(64)
+        self.check(self.lib.sphb200_peer_export(self.h, C.c_void_p(ptr), buf))
+        return buf.raw
+
+    def peer_open(self, handle):
+        p = C.c_void_p()
+        self.check(self.lib.sphb200_peer_open(self.h, C.create_string_buffer(bytes(handle), 64), C.byref(p)))
+        return p.value
+
+    def peer_close(self, ptr):
+        self.check(self.lib.sphb200_peer_close(self.h, C.c_void_p(ptr)))
+
+    def rows_push(self, src_ptr, row_bytes, idx_ptr, n, peer_landing, peer_flag, epoch):
+        self.check(self.lib.sphb200_rows_push(self.h, C.c_void_p(src_ptr), int(row_bytes), C.c_void_p(idx_ptr), int(n),
+                                              C.c_void_p(peer_landing), C.c_void_p(peer_flag), int(epoch)))
+
+    def rows_wait_scatter(self, dst_ptr, row_bytes, idx_ptr, n, landing, flag, epoch):
+        self.check(self.lib.sphb200_rows_wait_scatter(self.h, C.c_void_p(dst_ptr), int(row_bytes), C.c_void_p(idx_ptr), int(n),
+                                                      C.c_void_p(landing), C.c_void_p(flag), int(epoch)))
+
+    def peer_timeouts(self):
+        out = C.c_int64()
+        self.check(self.lib.sphb200_peer_timeouts(self.h, C.byref(out)))
+        return out.value
+
     def relaxation_state(self):
         out = (C.c_double * 5)()
         self.check(self.lib.sphb200_relaxation_state(self.h, out))

@@ -119,6 +119,11 @@ class LocalComm:
         """arrays: one host int64 array per local slab; returns their element-wise sum over all slabs"""
         return np.sum(np.stack(arrays), axis=0)
 
+    def peer_bases(self, systems, bases):
+        """(left, right) neighbour's landing allocation as seen from each local slab: same process, the pointer itself"""
+        n = len(bases)
+        return [(bases[k - 1] if k > 0 else None, bases[k + 1] if k + 1 < n else None) for k in range(n)]
+
     def allreduce_max_device(self, slots):
         """slots: one int64 device tensor per local slab (bit pattern of a non-negative double): all get the maximum"""
         if len(slots) > 1:
@@ -199,6 +204,16 @@ class DistComm:
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return t.cpu().numpy()
 
+    def peer_bases(self, systems, bases):
+        """every rank exports its landing allocation (cudaIpcGetMemHandle), the handles go round once, and each rank maps
+        its two neighbours' allocations into its own address space (cudaIpcOpenMemHandle, peer access over NVLink)"""
+        mine = torch.frombuffer(bytearray(systems[0].peer_export(bases[0])), dtype=torch.uint8).to(self.device)
+        everyone = [torch.empty_like(mine) for _ in range(self.world)]
+        dist.all_gather(everyone, mine)
+        def opened(r):
+            return systems[0].peer_open(bytes(everyone[r].cpu().numpy().tobytes())) if 0 <= r < self.world else None
+        return [(opened(self.rank - 1), opened(self.rank + 1))]
+
     def allreduce_max_device(self, slots):
         dist.all_reduce(slots[0], op=dist.ReduceOp.MAX)  # stays on the device: no host synchronisation
 
@@ -229,9 +244,11 @@ class SlabDamBreak:
     """tests/3d_examples/test_3d_dambreak/dambreak.cpp:159-195 over n_slabs slabs; same loop as cases.DamBreak"""
 
     def __init__(self, backend, comm, dp=0.05, real_bytes=8, device=0, stream=None, ndim=3, device_loop=True, fast_reconfigure=True,
-                 recut_interval=20, recut_threshold=0.05):
+                 recut_interval=20, recut_threshold=0.05, peer_halo=True):
         """recut_interval / recut_threshold: every recut_interval advection steps the owned fluid per page is summed over
         the slabs and, when the fullest slab holds more than (1 + threshold) x the mean, the cuts move (SURVEY 8e; 0 = never);
+        peer_halo: the per-sub-step halo records are pushed straight into the neighbour GPU's memory by the pack kernel
+        (csrc/peer.cu; False: pack -> torch.distributed send/recv -> unpack);
         device_loop: dt / relaxation time / exit test of the sub-step loop on the device (False: one host round trip
         per sub-step, the round-1 path); fast_reconfigure: sphb200_slab_select/pack/rebuild and one cell-list update
         per advection step (False: keep_range + two cell-list updates + torch.cat, the round-1 path)"""
@@ -291,6 +308,9 @@ class SlabDamBreak:
             c.update_configuration(observer=False)
             c.sys.gravity_force(w, c.gravity)
             self.parts.append(P)
+        self.peer_halo, self._epoch = bool(peer_halo), [0, 0]
+        if self.peer_halo:
+            self._peer_setup()
         self._halo_maps()
         self.time, self.dt, self.n_advection, self.n_acoustic = 0.0, 0.0, 0, 0
 
@@ -325,9 +345,54 @@ class SlabDamBreak:
             P.recv_buf = [torch.empty((ix.numel() if ix is not None else 0, 8), dtype=t_real, device=self.device)
                           for ix in (P.recv_left, P.recv_right)]
             P.slot = dev_tensor(P.case.sys.reduce_slot_ptr(0), (1,), np.int64, self.device)
+            if self.peer_halo:
+                for ix in (P.send_left, P.send_right, P.recv_left, P.recv_right):
+                    if ix is not None and ix.numel() > self._peer_rows:
+                        raise RuntimeError(f"halo page of {ix.numel()} rows exceeds the landing buffer ({self._peer_rows})")
+
+    # ---- halo records over peer memory -------------------------------------------------------------
+    def _peer_setup(self):
+        """one exportable allocation per slab: 4 flag words + 4 landing buffers ({from left, from right} x {rec_a, rec_b}),
+        each large enough for a completely filled cell page (a page cannot hold more than its volume / dp^3 particles, so
+        the buffers never have to grow and the sender needs no answer from the receiver)"""
+        per_page = int(np.prod(self.n_lat[1:])) * (int(math.ceil(self.spacing / self.dp)) + 1)
+        self._peer_rows = int(1.1 * per_page) + 1024
+        self._row_bytes = 8 * self.real_bytes
+        self._peer_flags = 256
+        nbytes = self._peer_flags + 4 * self._peer_rows * self._row_bytes
+        for P in self.parts:
+            P.peer_base = P.case.sys.peer_alloc(nbytes)
+        got = self.comm.peer_bases([P.case.sys for P in self.parts], [P.peer_base for P in self.parts])
+        for P, (left, right) in zip(self.parts, got):
+            P.peer_left, P.peer_right = (left if P.has_left else None), (right if P.has_right else None)
+
+    def _peer_slot(self, base, side, which):
+        """(landing buffer, flag word) of the area `side` (0: rows that came from the left, 1: from the right) of record `which`"""
+        k = side * 2 + which
+        return base + self._peer_flags + k * self._peer_rows * self._row_bytes, base + 8 * k
+
+    def _halo_records_peer(self, which):
+        self._epoch[which] += 1
+        ep = self._epoch[which]
+        for P in self.parts:            # every push is enqueued before any wait (one stream serves all slabs of a LocalComm)
+            S = P.case.sys
+            for side, ix, peer in ((0, P.send_left, P.peer_left), (1, P.send_right, P.peer_right)):
+                if peer is not None:
+                    landing, flag = self._peer_slot(peer, 1 - side, which)   # what I send left arrives "from the right"
+                    n = ix.numel()
+                    S.rows_push(P.rec_ptr[which], self._row_bytes, ix.data_ptr() if n else 0, n, landing, flag, ep)
+        for P in self.parts:
+            S = P.case.sys
+            for side, ix, there in ((0, P.recv_left, P.has_left), (1, P.recv_right, P.has_right)):
+                if there:
+                    landing, flag = self._peer_slot(P.peer_base, side, which)
+                    n = ix.numel()
+                    S.rows_wait_scatter(P.rec_ptr[which], self._row_bytes, ix.data_ptr() if n else 0, n, landing, flag, ep)
 
     def _halo_records(self, which):
         """owner's records of the rows in the neighbour's halo: pack (sphb200_rows_gather) -> send/recv -> unpack (rows_scatter)"""
+        if self.peer_halo:
+            return self._halo_records_peer(which)
         sends, rows = [], []
         row_bytes = 8 * self.real_bytes
         for P in self.parts:
@@ -395,6 +460,8 @@ class SlabDamBreak:
                     break
                 batch = 1
             k, self.dt, relaxation = st["substeps"], st["dt"], st["relaxation_time"]
+            if self.peer_halo and any(P.case.sys.peer_timeouts() for P in self.parts):
+                raise RuntimeError("a halo push from a neighbour slab did not arrive within the time-out")
             self._guess = k
             self.time += relaxation
             self.n_acoustic += k

@@ -113,11 +113,12 @@ def test_dist_comm_protocol_over_gloo(tmp_path):
                          [(2, 8, -1, False), (3, 8, 0, False), (2, 4, -1, False), (3, 4, 1, False), (4, 8, -1, False), (3, 8, -1, True)])
 def test_slabs_equal_single_gpu(pk, gpu, slab, n_slabs, real_bytes, pair_kernel, round1_path):
     """N slabs emulated in one process (LocalComm) against the undecomposed run; round1_path: host-driven sub-step
-    loop and the two-sort reconfigure instead of the device-resident loop and sphb200_slab_select/pack/rebuild"""
+    loop, the two-sort reconfigure and send/recv halo records instead of the device-resident loop,
+    sphb200_slab_select/pack/rebuild and the halo push into peer memory (sphb200_rows_push / rows_wait_scatter)"""
     dp, steps = 0.05, 8
     one = pk.cases.DamBreak(gpu, ndim=3, dp=dp, real_bytes=real_bytes, with_observer=False)
     many = slab.SlabDamBreak(gpu, slab.LocalComm(n_slabs), dp=dp, real_bytes=real_bytes, device_loop=not round1_path,
-                             fast_reconfigure=not round1_path)
+                             fast_reconfigure=not round1_path, peer_halo=not round1_path)
     one.sys.set_pair_kernel(pair_kernel)
     for P in many.parts:
         P.case.sys.set_pair_kernel(pair_kernel)
@@ -169,14 +170,17 @@ def _compare_owned_with_single(one, many, dp, tol):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n_slabs,recut_interval", [(3, 0), (3, 5), (4, 3)])
-def test_migration_and_recut_over_a_collapsing_column(pk, gpu, slab, n_slabs, recut_interval):
+@pytest.mark.parametrize("n_slabs,recut_interval,in_place,peer_halo", [(3, 0, True, True), (3, 5, True, True), (4, 3, True, False), (3, 5, False, True)])
+def test_migration_and_recut_over_a_collapsing_column(pk, gpu, slab, monkeypatch, n_slabs, recut_interval, in_place, peer_halo):
     """long enough for particles to cross the cuts (migrants must stay behind as the sender's halo copies) and, with
     recut_interval > 0, for the cuts themselves to follow the front (whole pages of fluid and wall change slabs):
     the decomposed run still equals the undecomposed one, halo sets included (checked through the sums)"""
     dp, steps = 0.05, 140
+    if not in_place:
+        monkeypatch.setenv("SPHB200_SLAB_INPLACE", "0")       # the gather path of sphb200_slab_rebuild
     one = pk.cases.DamBreak(gpu, ndim=3, dp=dp, real_bytes=8, with_observer=False)
-    many = slab.SlabDamBreak(gpu, slab.LocalComm(n_slabs), dp=dp, real_bytes=8, recut_interval=recut_interval, recut_threshold=0.0)
+    many = slab.SlabDamBreak(gpu, slab.LocalComm(n_slabs), dp=dp, real_bytes=8, recut_interval=recut_interval, recut_threshold=0.0,
+                             peer_halo=peer_halo)
     pos0 = one.water.get("Position").astype(np.float64)
     oid0, _ = one.water.ids()
     idx = np.rint((pos0 - many.sys_lo) / dp - 0.5).astype(np.int64)
