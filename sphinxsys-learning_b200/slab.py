@@ -19,6 +19,7 @@ memory, buffers, torch.distributed (NCCL) send/recv and all-reduce.
 slab per process.
 """
 import math
+import os
 
 import numpy as np
 
@@ -244,11 +245,11 @@ class SlabDamBreak:
     """tests/3d_examples/test_3d_dambreak/dambreak.cpp:159-195 over n_slabs slabs; same loop as cases.DamBreak"""
 
     def __init__(self, backend, comm, dp=0.05, real_bytes=8, device=0, stream=None, ndim=3, device_loop=True, fast_reconfigure=True,
-                 recut_interval=20, recut_threshold=0.05, peer_halo=True):
+                 recut_interval=20, recut_threshold=0.05, peer_halo=None):
         """recut_interval / recut_threshold: every recut_interval advection steps the owned fluid per page is summed over
         the slabs and, when the fullest slab holds more than (1 + threshold) x the mean, the cuts move (SURVEY 8e; 0 = never);
         peer_halo: the per-sub-step halo records are pushed straight into the neighbour GPU's memory by the pack kernel
-        (csrc/peer.cu; False: pack -> torch.distributed send/recv -> unpack);
+        (csrc/peer.cu; False: pack -> torch.distributed send/recv -> unpack; None: on unless env SPHB200_PEER_HALO=0);
         device_loop: dt / relaxation time / exit test of the sub-step loop on the device (False: one host round trip
         per sub-step, the round-1 path); fast_reconfigure: sphb200_slab_select/pack/rebuild and one cell-list update
         per advection step (False: keep_range + two cell-list updates + torch.cat, the round-1 path)"""
@@ -308,6 +309,8 @@ class SlabDamBreak:
             c.update_configuration(observer=False)
             c.sys.gravity_force(w, c.gravity)
             self.parts.append(P)
+        if peer_halo is None:
+            peer_halo = os.environ.get("SPHB200_PEER_HALO", "1") != "0"
         self.peer_halo, self._epoch = bool(peer_halo), [0, 0]
         if self.peer_halo:
             self._peer_setup()
