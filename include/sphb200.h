@@ -234,6 +234,24 @@ sphb200_status sphb200_ck_linear_correction_matrix(sphb200_relation *inner, sphb
 /* FreeSurfaceIndicationCK<Inner<WithUpdate>> + <Contact> (general_dynamics/surface_indication/surface_indication_ck.hpp:55-170): variables
  * "PositionDivergence", "Indicator", "PreviousSurfaceIndicator" (the reference's int variables are Real-typed 0 / 1 here) */
 sphb200_status sphb200_ck_free_surface_indication(sphb200_relation *inner, sphb200_relation *contact_or_null);
+/* The CK acoustic sub-step with linear kernel correction - the scheme of tests/tests_sycl/.../test_3d_dambreak_sycl and its 2-D
+ * twin (state: Compression, CompressionRate, Displacement; Position is committed once per advection step):
+ *   ck_advection_step_setup        AdvectionStepSetup::UpdateKernel (fluid_time_step_ck.h:145-148): Vol = m / rho, Displacement = 0
+ *   ck_update_particle_position    UpdateParticlePosition::UpdateKernel (fluid_time_step_ck.h:173-175): Position += Displacement
+ *   ck_acoustic_dt                 ReduceDynamicsCK<AcousticTimeStepCK> (fluid_time_step_ck.hpp:31-35,52-56):
+ *                                  cfl h / (max_i max(c0 + |v|, sqrt(4 h |F + Fp| / m)) + tiny)
+ *   ck_advection_dt                ReduceDynamicsCK<AdvectionTimeStepCK> (fluid_time_step_ck.cpp:23-25, .h:106-108)
+ *   ck_acoustic_step_1st_half      InteractionDynamicsCK<AcousticStep1stHalfWithWallRiemannCorrectionCK>::exec(dt)
+ *                                  (acoustic_step_1st_half.hpp:66-74,89-111,122-127,157-180); needs LinearCorrectionMatrix
+ *   ck_acoustic_step_2nd_half      ...2ndHalf... (acoustic_step_2nd_half.hpp:33-38,53-73,83-89,117-137)
+ * wall_or_null: contact relation to Solid walls (their Velocity / Acceleration are the averages the wall model reads,
+ * base_material.cpp:57-65; absent = zero; NormalDirection is required by the 2nd half). */
+sphb200_status sphb200_ck_advection_step_setup(sphb200_body *body);
+sphb200_status sphb200_ck_update_particle_position(sphb200_body *body);
+sphb200_status sphb200_ck_acoustic_dt(sphb200_body *body, double cfl, double *dt_out);
+sphb200_status sphb200_ck_advection_dt(sphb200_body *body, double U_ref, double cfl, double *dt_out);
+sphb200_status sphb200_ck_acoustic_step_1st_half(sphb200_relation *inner, sphb200_relation *wall_or_null, double dt);
+sphb200_status sphb200_ck_acoustic_step_2nd_half(sphb200_relation *inner, sphb200_relation *wall_or_null, double dt);
 
 /* ---- total-Lagrangian elastic solid -------------------------------------------------------- */
 /* LinearGradientCorrectionMatrix<Inner<>> (general_dynamics/kernel_correction.cpp:8-29) */

@@ -46,7 +46,9 @@ def load():
         "orc_transport_velocity_correction": (None, [vp, i, d]),
         "orc_total_kinetic_energy": (d, [vp, i]), "orc_total_mechanical_energy": (d, [vp, i, dp]),
         "orc_ck_density_regularization": (None, [vp, i, i, i]), "orc_ck_linear_correction_matrix": (None, [vp, i, i, d]),
-        "orc_ck_free_surface_indication": (None, [vp, i, i]), "orc_maximum_speed": (d, [vp, i]), "orc_position_bound": (None, [vp, i, i, dp]), "orc_observe": (None, [vp, i, cp, i, dp]),
+        "orc_ck_free_surface_indication": (None, [vp, i, i]), "orc_ck_advection_step_setup": (None, [vp, i]),
+        "orc_ck_update_particle_position": (None, [vp, i]), "orc_ck_acoustic_dt": (d, [vp, i, d]), "orc_ck_advection_dt": (d, [vp, i, d, d]),
+        "orc_ck_acoustic_1st_half": (None, [vp, i, i, d]), "orc_ck_acoustic_2nd_half": (None, [vp, i, i, d]), "orc_maximum_speed": (d, [vp, i]), "orc_position_bound": (None, [vp, i, i, dp]), "orc_observe": (None, [vp, i, cp, i, dp]),
         "orc_correction_matrix": (None, [vp, i]), "orc_solid_1st_half": (None, [vp, i, i, d]),
         "orc_solid_2nd_half": (None, [vp, i, d]), "orc_solid_constrain": (None, [vp, i, lp, l]),
         "orc_solid_dt": (d, [vp, i, d]), "orc_num_threads": (i, []), "orc_set_num_threads": (i, [i]),
@@ -138,6 +140,24 @@ class SPHSystem:
 
     def ck_linear_correction_matrix(self, inner, contact=None, alpha=0.0):
         self.lib.orc_ck_linear_correction_matrix(self.h, inner.id, contact.id if contact else -1, alpha)
+
+    def ck_advection_step_setup(self, body):
+        self.lib.orc_ck_advection_step_setup(self.h, body.id)
+
+    def ck_update_particle_position(self, body):
+        self.lib.orc_ck_update_particle_position(self.h, body.id)
+
+    def ck_acoustic_dt(self, body, cfl=0.6):
+        return self.lib.orc_ck_acoustic_dt(self.h, body.id, cfl)
+
+    def ck_advection_dt(self, body, U_ref, cfl=0.25):
+        return self.lib.orc_ck_advection_dt(self.h, body.id, U_ref, cfl)
+
+    def ck_acoustic_1st_half(self, inner, wall=None, dt=0.0):
+        self.lib.orc_ck_acoustic_1st_half(self.h, inner.id, wall.id if wall else -1, dt)
+
+    def ck_acoustic_2nd_half(self, inner, wall=None, dt=0.0):
+        self.lib.orc_ck_acoustic_2nd_half(self.h, inner.id, wall.id if wall else -1, dt)
 
     def ck_free_surface_indication(self, inner, contact=None):
         self.lib.orc_ck_free_surface_indication(self.h, inner.id, contact.id if contact else -1)

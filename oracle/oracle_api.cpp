@@ -349,6 +349,28 @@ void orc_ck_free_surface_indication(void *sys, int inner, int contact)
 {
     DISPATCH(sys, freeSurfaceIndicationCK<D, R>(*S.rels[inner], contact >= 0 ? S.rels[contact].get() : nullptr));
 }
+void orc_ck_advection_step_setup(void *sys, int body) { DISPATCH(sys, ckAdvectionStepSetup<D, R>(*S.bodies[body])); }
+void orc_ck_update_particle_position(void *sys, int body) { DISPATCH(sys, ckUpdateParticlePosition<D, R>(*S.bodies[body])); }
+double orc_ck_acoustic_dt(void *sys, int body, double cfl)
+{
+    double r = 0;
+    DISPATCH(sys, r = double(ckAcousticDt<D, R>(*S.bodies[body], R(cfl))));
+    return r;
+}
+double orc_ck_advection_dt(void *sys, int body, double U_ref, double cfl)
+{
+    double r = 0;
+    DISPATCH(sys, r = double(ckAdvectionDt<D, R>(*S.bodies[body], R(U_ref), R(cfl))));
+    return r;
+}
+void orc_ck_acoustic_1st_half(void *sys, int inner, int wall, double dt)
+{
+    DISPATCH(sys, ckAcoustic1stHalf<D, R>(*S.rels[inner], wall >= 0 ? S.rels[wall].get() : nullptr, R(dt)));
+}
+void orc_ck_acoustic_2nd_half(void *sys, int inner, int wall, double dt)
+{
+    DISPATCH(sys, ckAcoustic2ndHalf<D, R>(*S.rels[inner], wall >= 0 ? S.rels[wall].get() : nullptr, R(dt)));
+}
 void orc_position_bound(void *sys, int body, int upper, double *out3)
 {
     DISPATCH(sys, positionBound<D, R>(*S.bodies[body], upper != 0, out3));

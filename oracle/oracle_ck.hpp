@@ -258,4 +258,249 @@ void freeSurfaceIndicationCK(Relation<D, R> &inner, Relation<D, R> *contact)
     for (long i = 0; i < n; ++i)
         ind[i] = prev[i] = out[size_t(i)];
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// CK acoustic sub-step with linear kernel correction, as the SYCL dam-break mains run it:
+//   AdvectionStepSetup / UpdateParticlePosition   shared_ck/particle_dynamics/fluid_dynamics/fluid_time_step_ck.h:145-148,173-175
+//   AcousticTimeStepCK / AdvectionTimeStepCK      fluid_time_step_ck.hpp:31-35,52-56 ; fluid_time_step_ck.cpp:23-25 ; .h:106-108
+//   AcousticStep1stHalf<Inner<OneLevel, AcousticRiemannSolverCK, LinearCorrectionCK>> + <Contact<Wall, ...>>
+//                                                 acoustic_step_1st_half.hpp:66-74,89-111,122-127,157-180
+//   AcousticStep2ndHalf<Inner<...>> + <Contact<Wall, ...>>   acoustic_step_2nd_half.hpp:33-38,53-73,83-89,117-137
+// The state is (Compression, CompressionRate, Displacement) instead of the classic (Density, DensityChangeRate, Position):
+// Position is not touched inside the sub-steps, so W, dW, e are those of the configuration.
+// ---------------------------------------------------------------------------------------------------------------
+template <int D, class R>
+void ckAdvectionStepSetup(Body<D, R> &b)
+{
+    R *Vol = b.v("VolumetricMeasure"), *mass = b.v("Mass"), *rho = b.v("Density"), *dpos = b.v("Displacement", D);
+    for (size_t i = 0; i < b.n; ++i)
+    {
+        Vol[i] = mass[i] / rho[i];
+        for (int a = 0; a < D; ++a)
+            dpos[i * D + a] = R(0);
+    }
+}
+template <int D, class R>
+void ckUpdateParticlePosition(Body<D, R> &b)
+{
+    R *pos = b.v("Position", D), *dpos = b.v("Displacement", D);
+    for (size_t i = 0; i < b.n * D; ++i)
+        pos[i] += dpos[i];
+}
+template <int D, class R>
+R ckAcousticDt(Body<D, R> &b, R cfl)
+{
+    const R *mass = b.v("Mass"), *vel = b.v("Velocity", D), *F = b.v("Force", D), *Fp = b.v("ForcePrior", D);
+    R red = R(0);
+    for (size_t i = 0; i < b.n; ++i)
+    {
+        R f[D];
+        for (int a = 0; a < D; ++a)
+            f[a] = F[i * D + a] + Fp[i * D + a];
+        const R acc_scale = std::sqrt(R(4.0) * b.h * std::sqrt(sqnorm<D, R>(f)) / mass[i]);
+        red = std::max(red, std::max(R(b.mat.c0) + std::sqrt(sqnorm<D, R>(vel + i * D)), acc_scale));
+    }
+    return cfl * b.h / (red + Tiny<R>::value);
+}
+template <int D, class R>
+R ckAdvectionDt(Body<D, R> &b, R U_ref, R cfl)
+{
+    const R *vel = b.v("Velocity", D);
+    R red = R(0);
+    for (size_t i = 0; i < b.n; ++i)
+        red = std::max(red, sqnorm<D, R>(vel + i * D));
+    return cfl * b.h / (std::max(std::sqrt(red), U_ref) + Tiny<R>::value);
+}
+template <int D, class R>
+inline void matVec(const R *B, const R *e, R *out)
+{
+    for (int a = 0; a < D; ++a)
+    {
+        out[a] = R(0);
+        for (int c = 0; c < D; ++c)
+            out[a] += B[a * D + c] * e[c];
+    }
+}
+
+template <int D, class R>
+void ckAcoustic1stHalf(Relation<D, R> &inner, Relation<D, R> *wall, R dt)
+{
+    Body<D, R> &b = *inner.body;
+    const long n = long(b.n);
+    const R rho0 = R(b.mat.rho0), c0 = R(b.mat.c0);
+    Riemann<R> rs(rho0, c0, true);
+    if (b.vars.find("Compression") == b.vars.end())
+    { // registerStateVariable<Real>("Compression", Real(1)), acoustic_step_1st_half.hpp:20
+        R *c = b.v("Compression");
+        for (long i = 0; i < n; ++i)
+            c[i] = R(1);
+    }
+    const R *pos = b.v("Position", D), *Vol = b.v("VolumetricMeasure"), *mass = b.v("Mass"), *Bm = b.v("LinearCorrectionMatrix", D * D),
+            *Fp = b.v("ForcePrior", D);
+    R *rho = b.v("Density"), *p = b.v("Pressure"), *comp = b.v("Compression"), *crate = b.v("CompressionRate"), *vel = b.v("Velocity", D),
+      *dpos = b.v("Displacement", D), *F = b.v("Force", D);
+    for (long i = 0; i < n; ++i) // InitializeKernel
+    {
+        comp[i] += R(0.5) * dt * crate[i];
+        rho[i] = comp[i] * rho0;
+        p[i] = rho0 * c0 * c0 * (rho[i] / rho0 - R(1.0)); // weakly_compressible_fluid.hpp getPressure
+        for (int a = 0; a < D; ++a)
+            dpos[i * D + a] += vel[i * D + a] * dt * R(0.5);
+    }
+    const TabKernel<D, R> k(b.h, b.h);
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < n; ++i) // InteractKernel, inner
+    {
+        R fs[D] = {}, diss = R(0);
+        const auto &nb = inner.configs[0][i];
+        for (size_t m = 0; m != nb.current_size; ++m)
+        {
+            const size_t j = nb.j[m];
+            R d[D], e[D], M[D * D], Me[D];
+            const R r = dispNorm<D, R>(pos + i * D, pos + j * D, d);
+            const R dWV = k.dW(r) * Vol[j];
+            for (int a = 0; a < D; ++a)
+                e[a] = d[a] / r;
+            // AverageP(B_j p_i, B_i p_j) * 2 = B_j p_i + B_i p_j   (riemann_solver_ck: average = half the sum)
+            for (int q = 0; q < D * D; ++q)
+                M[q] = R(0.5) * (Bm[j * D * D + q] * p[i] + Bm[i * D * D + q] * p[j]);
+            matVec<D, R>(M, e, Me);
+            for (int a = 0; a < D; ++a)
+                fs[a] -= Me[a] * R(2.0) * dWV;
+            diss += rs.UJump(p[i] - p[j]) * dWV;
+        }
+        for (int a = 0; a < D; ++a)
+            F[i * D + a] += fs[a] * Vol[i];
+        crate[i] = diss * comp[i];
+    }
+    if (wall)
+        for (size_t t = 0; t < wall->targets.size(); ++t)
+        {
+            Body<D, R> &tb = *wall->targets[t];
+            const R *tpos = tb.v("Position", D), *tvol = tb.v("VolumetricMeasure"), *tacc = tb.v("Acceleration", D);
+            const TabKernel<D, R> kc(b.h, tb.h);
+#pragma omp parallel for schedule(static)
+            for (long i = 0; i < n; ++i)
+            {
+                R fs[D] = {}, diss = R(0);
+                const auto &cn = wall->configs[t][i];
+                for (size_t m = 0; m != cn.current_size; ++m)
+                {
+                    const size_t j = cn.j[m];
+                    R d[D], e[D], Be[D];
+                    const R r = dispNorm<D, R>(pos + i * D, tpos + j * D, d);
+                    const R dWV = kc.dW(r) * tvol[j];
+                    R face = R(0);
+                    for (int a = 0; a < D; ++a)
+                    {
+                        e[a] = d[a] / r;
+                        face += (Fp[i * D + a] / mass[i] - tacc[j * D + a]) * (-e[a]);
+                    }
+                    const R p_wall = p[i] + rho[i] * r * std::max(R(0), face);
+                    matVec<D, R>(Bm + i * D * D, e, Be);
+                    for (int a = 0; a < D; ++a)
+                        fs[a] -= (p[i] + p_wall) * Be[a] * dWV;
+                    diss += rs.UJump(p[i] - p_wall) * dWV;
+                }
+                for (int a = 0; a < D; ++a)
+                    F[i * D + a] += fs[a] * Vol[i];
+                crate[i] += diss * comp[i];
+            }
+        }
+    for (long i = 0; i < n; ++i) // UpdateKernel
+        for (int a = 0; a < D; ++a)
+            vel[i * D + a] += (Fp[i * D + a] + F[i * D + a]) / mass[i] * dt;
+}
+
+template <int D, class R>
+void ckAcoustic2ndHalf(Relation<D, R> &inner, Relation<D, R> *wall, R dt)
+{
+    Body<D, R> &b = *inner.body;
+    const long n = long(b.n);
+    const R rho0 = R(b.mat.rho0), c0 = R(b.mat.c0);
+    Riemann<R> rs(rho0, c0, true);
+    const R *pos = b.v("Position", D), *Vol = b.v("VolumetricMeasure"), *Bm = b.v("LinearCorrectionMatrix", D * D), *vel = b.v("Velocity", D);
+    R *rho = b.v("Density"), *comp = b.v("Compression"), *crate = b.v("CompressionRate"), *dpos = b.v("Displacement", D), *F = b.v("Force", D);
+    for (long i = 0; i < n * D; ++i) // InitializeKernel
+        dpos[i] += vel[i] * dt * R(0.5);
+    const TabKernel<D, R> k(b.h, b.h);
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < n; ++i)
+    {
+        R div = R(0), pd[D] = {}, Be[D];
+        const auto &nb = inner.configs[0][i];
+        for (size_t m = 0; m != nb.current_size; ++m)
+        {
+            const size_t j = nb.j[m];
+            R d[D], e[D];
+            const R r = dispNorm<D, R>(pos + i * D, pos + j * D, d);
+            const R dWV = k.dW(r) * Vol[j];
+            for (int a = 0; a < D; ++a)
+                e[a] = d[a] / r;
+            matVec<D, R>(Bm + i * D * D, e, Be);
+            R dvBe = R(0), u = R(0);
+            for (int a = 0; a < D; ++a)
+            {
+                const R vave = R(0.5) * (vel[i * D + a] + vel[j * D + a]); // AverageV
+                dvBe += R(2.0) * (vel[i * D + a] - vave) * Be[a];
+                u += (vel[i * D + a] - vel[j * D + a]) * e[a];
+            }
+            div += dvBe * dWV;
+            const R pj = rs.PJump(u) * dWV;
+            for (int a = 0; a < D; ++a)
+                pd[a] += pj * e[a];
+        }
+        crate[i] += div * comp[i];
+        for (int a = 0; a < D; ++a)
+            F[i * D + a] = pd[a] * Vol[i];
+    }
+    if (wall)
+        for (size_t t = 0; t < wall->targets.size(); ++t)
+        {
+            Body<D, R> &tb = *wall->targets[t];
+            const R *tpos = tb.v("Position", D), *tvol = tb.v("VolumetricMeasure"), *tvel = tb.v("Velocity", D), *tn = tb.v("NormalDirection", D);
+            const TabKernel<D, R> kc(b.h, tb.h);
+#pragma omp parallel for schedule(static)
+            for (long i = 0; i < n; ++i)
+            {
+                R div = R(0), pd[D] = {}, Be[D];
+                const auto &cn = wall->configs[t][i];
+                for (size_t m = 0; m != cn.current_size; ++m)
+                {
+                    const size_t j = cn.j[m];
+                    R d[D], e[D], vd[D], nf[D];
+                    const R r = dispNorm<D, R>(pos + i * D, tpos + j * D, d);
+                    const R dWV = kc.dW(r) * tvol[j];
+                    R en = R(0);
+                    for (int a = 0; a < D; ++a)
+                    {
+                        e[a] = d[a] / r;
+                        vd[a] = R(2.0) * (vel[i * D + a] - tvel[j * D + a]);
+                        en += e[a] * tn[j * D + a];
+                    }
+                    matVec<D, R>(Bm + i * D * D, e, Be);
+                    const R sgn = en > R(0) ? R(1) : (en < R(0) ? R(-1) : R(0)); // SGN: common/scalar_functions.h:127-131
+                    R dvBe = R(0), u = R(0);
+                    for (int a = 0; a < D; ++a)
+                    {
+                        nf[a] = sgn * tn[j * D + a];
+                        dvBe += vd[a] * Be[a];
+                        u += vd[a] * nf[a];
+                    }
+                    div += dvBe * dWV;
+                    const R pj = rs.PJump(u) * dWV;
+                    for (int a = 0; a < D; ++a)
+                        pd[a] += pj * nf[a];
+                }
+                crate[i] += div * comp[i];
+                for (int a = 0; a < D; ++a)
+                    F[i * D + a] += pd[a] * Vol[i];
+            }
+        }
+    for (long i = 0; i < n; ++i) // UpdateKernel
+    {
+        comp[i] += R(0.5) * dt * crate[i];
+        rho[i] = comp[i] * rho0;
+    }
+}
 } // namespace orc

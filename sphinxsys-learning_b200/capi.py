@@ -99,6 +99,12 @@ SIGNATURES = {
     "sphb200_ck_density_regularization": (_i, [_vp, _vp, _i]),
     "sphb200_ck_linear_correction_matrix": (_i, [_vp, _vp, _d]),
     "sphb200_ck_free_surface_indication": (_i, [_vp, _vp]),
+    "sphb200_ck_advection_step_setup": (_i, [_vp]),
+    "sphb200_ck_update_particle_position": (_i, [_vp]),
+    "sphb200_ck_acoustic_dt": (_i, [_vp, _d, _dp]),
+    "sphb200_ck_advection_dt": (_i, [_vp, _d, _d, _dp]),
+    "sphb200_ck_acoustic_step_1st_half": (_i, [_vp, _vp, _d]),
+    "sphb200_ck_acoustic_step_2nd_half": (_i, [_vp, _vp, _d]),
     "sphb200_correction_matrix": (_i, [_vp]),
     "sphb200_solid_1st_half": (_i, [_vp, _i, _d]),
     "sphb200_solid_2nd_half": (_i, [_vp, _d]),

@@ -221,6 +221,85 @@ class DamBreak:
         return self.sys.observe(self.obs_contact, "Pressure", 1)
 
 
+class DamBreakCK(DamBreak):
+    """The CK-flavour dam break: tests/tests_sycl/3d_examples/test_3d_dambreak_sycl/dambreak.cpp:183-222 (ndim = 3) and
+    tests/tests_sycl/2d_examples/test_2d_dambreak_sycl/dambreak_sycl.cpp:170-240 (ndim = 2).  Same bodies as the classic
+    case; the dynamics are CompressionSummation + DensityRegularization, AdvectionStepSetup, the spatial-temporal free
+    surface indication (3-D main only), LinearCorrectionMatrix(0.5) and the corrected acoustic steps on
+    (Compression, CompressionRate, Displacement), all with the tabulated kernel."""
+
+    def __init__(self, backend, ndim=3, dp=0.05, real_bytes=8, with_observer=True, **kw):
+        super().__init__(backend, ndim=ndim, dp=dp, real_bytes=real_bytes, with_observer=with_observer, **kw)
+        w = self.water
+        for name, width in (("Displacement", ndim), ("Compression", 1), ("CompressionRate", 1)):
+            w.register(name, width, True)
+        w.set("Compression", np.ones(w.n, np.float64 if real_bytes == 8 else np.float32))
+        self.advection_steps = 1
+        if ndim == 2:   # dambreak_sycl.cpp:150-156: the first advection step's preparation happens before the loop
+            self._prepare_2d()
+            self._interval, self._present = self.sys.ck_advection_dt(w, self.U_ref), 0.0
+
+    def _prepare_2d(self):
+        S = self.sys
+        S.ck_density_regularization(self.inner, self.wall_contact, True)
+        S.ck_advection_step_setup(self.water)
+        S.ck_linear_correction_matrix(self.inner, self.wall_contact, 0.5)
+
+    def advection_step(self, sort_interval=100, observer=True, before_configuration=None):
+        """3-D main: one outer iteration (dambreak.cpp:187-222); returns (Dt, sub-steps)"""
+        assert self.ndim == 3
+        S, w = self.sys, self.water
+        S.ck_density_regularization(self.inner, self.wall_contact, True)
+        S.ck_advection_step_setup(w)
+        Dt = S.ck_advection_dt(w, self.U_ref)
+        S.ck_free_surface_indication(self.inner, self.wall_contact)
+        S.ck_linear_correction_matrix(self.inner, self.wall_contact, 0.5)
+        relaxation, k = 0.0, 0
+        while relaxation < Dt:
+            self.dt = S.ck_acoustic_dt(w)
+            S.ck_acoustic_1st_half(self.inner, self.wall_contact, self.dt)
+            S.ck_acoustic_2nd_half(self.inner, self.wall_contact, self.dt)
+            relaxation += self.dt
+            self.time += self.dt
+            k += 1
+        self.n_acoustic += k
+        S.ck_update_particle_position(w)
+        if before_configuration is not None:
+            before_configuration()
+        self.n_advection += 1
+        if sort_interval and self.n_advection % sort_interval == 0 and self.n_advection != 1:
+            w.sort()
+        w.update_cell_list()
+        self.update_configuration(observer)
+        return Dt, k
+
+    def acoustic_step_2d(self, on_advection=None):
+        """2-D main: one iteration of its single loop (dambreak_sycl.cpp:176-228): an acoustic step, and the advection-step
+        work whenever the accumulated time passes the interval; returns True when an advection step was completed"""
+        assert self.ndim == 2
+        S, w = self.sys, self.water
+        self.dt = S.ck_acoustic_dt(w)
+        self.time += self.dt
+        self._present += self.dt
+        S.ck_acoustic_1st_half(self.inner, self.wall_contact, self.dt)
+        S.ck_acoustic_2nd_half(self.inner, self.wall_contact, self.dt)
+        self.n_acoustic += 1
+        if self._present <= self._interval:
+            return False
+        self._present, self._interval = 0.0, S.ck_advection_dt(w, self.U_ref)
+        self.advection_steps += 1
+        self.n_advection += 1
+        S.ck_update_particle_position(w)
+        if on_advection is not None:
+            on_advection()
+        if self.advection_steps % 100:   # sic (dambreak_sycl.cpp:214): order only, the results do not depend on it
+            w.sort()
+        w.update_cell_list()
+        self.update_configuration(self.observer is not None)
+        self._prepare_2d()
+        return True
+
+
 # ------------------------------------------------------------------------------------------------
 # 2-D Taylor-Green vortex
 # ------------------------------------------------------------------------------------------------

@@ -238,6 +238,319 @@ __global__ void __launch_bounds__(256) k_ck_fill(int64_t n, R value, R *__restri
         a[i] = value;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// CK acoustic sub-step with LinearCorrectionCK (the scheme of tests_sycl/.../test_3d_dambreak_sycl and its 2-D twin):
+//   AdvectionStepSetup / UpdateParticlePosition     fluid_time_step_ck.h:145-148,173-175
+//   AcousticTimeStepCK / AdvectionTimeStepCK        fluid_time_step_ck.hpp:31-35,52-56 ; .cpp:23-25 ; .h:106-108
+//   AcousticStep1stHalf<Inner<OneLevel, AcousticRiemannSolverCK, LinearCorrectionCK>> + <Contact<Wall, ...>>
+//                                                   acoustic_step_1st_half.hpp:66-74,89-111,122-127,157-180
+//   AcousticStep2ndHalf<...>                        acoustic_step_2nd_half.hpp:33-38,53-73,83-89,117-137
+// State: Compression / CompressionRate / Displacement (Position is committed once per advection step, so the pair
+// geometry is the configuration's, as in the reference where the sub-steps never touch Position).
+// ---------------------------------------------------------------------------------------------------------------
+template <int D, class R>
+struct CkRiemann
+{
+    R inv_rho0c0, rho0c0, inv_c0; // riemann_solver.h:55-123 with both sides the same fluid
+};
+template <class R>
+__device__ __forceinline__ R ckPJump(R rho0c0, R inv_c0, R u) { return rho0c0 * u * fmin(R(3.0) * (inv_c0 * fmax(u, R(0))), R(1)); }
+
+template <int D, class R>
+__global__ void __launch_bounds__(256) k_ck_setup(int64_t i0, int64_t n, const R *__restrict__ mass, const R *__restrict__ rho,
+                                                  R *__restrict__ Vol, R *__restrict__ dpos)
+{
+    const int64_t i = i0 + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    Vol[i] = mass[i] / rho[i];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        dpos[i * D + a] = R(0);
+}
+template <class R>
+__global__ void __launch_bounds__(256) k_ck_axpy(int64_t e0, int64_t e1, R *__restrict__ y, const R *__restrict__ x)
+{
+    const int64_t e = e0 + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (e < e1)
+        y[e] += x[e];
+}
+// kind 0: max(c0 + |v|, sqrt(4 h |F + Fp| / m));  kind 1: max |v|^2
+template <int D, class R>
+__global__ void __launch_bounds__(256)
+    k_ck_dt_max(int64_t i0, int64_t n, int kind, R c0, R h, const R *__restrict__ vel, const R *__restrict__ force, const R *__restrict__ fprior,
+                const R *__restrict__ mass, unsigned long long *__restrict__ slot)
+{
+    int64_t i = i0 + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    R s = R(0);
+    for (; i < n; i += int64_t(gridDim.x) * blockDim.x)
+    {
+        R v[D], f[D];
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+        {
+            v[a] = vel[i * D + a];
+            f[a] = kind == 0 ? force[i * D + a] + fprior[i * D + a] : R(0);
+        }
+        if (kind == 0)
+        {
+            const R acc_scale = sqrt_r(R(4.0) * h * sqrt_r(sqnormExact<D, R>(f)) / mass[i]);
+            s = fmax(s, fmax(c0 + sqrt_r(sqnormExact<D, R>(v)), acc_scale));
+        }
+        else
+            s = fmax(s, sqnormExact<D, R>(v));
+    }
+    s = warpMax<R>(s);
+    if ((threadIdx.x & 31) == 0)
+        atomicMaxNonNeg(slot, double(s));
+}
+template <int D, class R>
+__global__ void __launch_bounds__(256)
+    k_ck_first_init(int64_t i0, int64_t n, R dt, R rho0, R c0, R *__restrict__ comp, const R *__restrict__ crate, R *__restrict__ rho,
+                    R *__restrict__ p, const R *__restrict__ vel, R *__restrict__ dpos)
+{
+    const int64_t i = i0 + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    const R c = comp[i] + R(0.5) * dt * crate[i];
+    comp[i] = c;
+    const R r = c * rho0;
+    rho[i] = r;
+    p[i] = rho0 * c0 * c0 * (r / rho0 - R(1.0));
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        dpos[i * D + a] += vel[i * D + a] * dt * R(0.5);
+}
+template <int D, class R>
+__device__ __forceinline__ void ckMatVec(const R *__restrict__ B, const R *e, R *out)
+{
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+    {
+        out[a] = R(0);
+#pragma unroll
+        for (int c = 0; c < D; ++c)
+            out[a] += B[a * D + c] * e[c];
+    }
+}
+template <int D, class R>
+__global__ void __launch_bounds__(128)
+    k_ck_first_inner(int64_t i0, int64_t n, const typename Real4<R>::type *__restrict__ xV, CkList in, TabKernelP<R> k, CkRiemann<D, R> rs,
+                     const R *__restrict__ p, const R *__restrict__ B, const R *__restrict__ Vol, const R *__restrict__ comp,
+                     R *__restrict__ crate, R *__restrict__ force)
+{
+    CK_INDEX();
+    const R pi = p[i];
+    R Bi[D * D];
+#pragma unroll
+    for (int q = 0; q < D * D; ++q)
+        Bi[q] = B[i * D * D + q];
+    R fs[D] = {}, diss = R(0);
+    const u32 cnt = in.count[i];
+    const u32 *lst = listBase(in.list, in.slice_off, i);
+    for (u32 m = 0; m < cnt; ++m)
+    {
+        const u32 j = listEntry(lst, m);
+        R d[D], Vj, e[D], M[D * D], Me[D];
+        const R r = ckDisp<D, R>(xi, xV, j, d, Vj);
+        const R dWV = tabdW<D, R>(k, r) * Vj;
+        const R pj = p[j];
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            e[a] = d[a] / r;
+#pragma unroll
+        for (int q = 0; q < D * D; ++q)
+            M[q] = R(0.5) * (B[int64_t(j) * D * D + q] * pi + Bi[q] * pj);
+        ckMatVec<D, R>(M, e, Me);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            fs[a] -= Me[a] * R(2.0) * dWV;
+        diss += (pi - pj) * rs.inv_rho0c0 * dWV;
+    }
+    const R Vi = Vol[i];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        force[i * D + a] += fs[a] * Vi;
+    crate[i] = diss * comp[i];
+}
+template <int D, class R>
+__global__ void __launch_bounds__(128)
+    k_ck_first_wall(int64_t i0, int64_t n, const typename Real4<R>::type *__restrict__ xV, const typename Real4<R>::type *__restrict__ xV_t,
+                    CkList in, TabKernelP<R> k, CkRiemann<D, R> rs, const R *__restrict__ p, const R *__restrict__ rho, const R *__restrict__ mass,
+                    const R *__restrict__ fprior, const R *__restrict__ wall_acc, const R *__restrict__ B, const R *__restrict__ Vol,
+                    const R *__restrict__ comp, R *__restrict__ crate, R *__restrict__ force)
+{
+    CK_INDEX();
+    const u32 cnt = in.count[i];
+    if (cnt == 0)
+        return;
+    const R pi = p[i], rhoi = rho[i];
+    R Bi[D * D], acc[D];
+#pragma unroll
+    for (int q = 0; q < D * D; ++q)
+        Bi[q] = B[i * D * D + q];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        acc[a] = fprior[i * D + a] / mass[i];
+    R fs[D] = {}, diss = R(0);
+    const u32 *lst = listBase(in.list, in.slice_off, i);
+    for (u32 m = 0; m < cnt; ++m)
+    {
+        const u32 j = listEntry(lst, m);
+        R d[D], Vj, e[D], Be[D];
+        const R r = ckDisp<D, R>(xi, xV_t, j, d, Vj);
+        const R dWV = tabdW<D, R>(k, r) * Vj;
+        R face = R(0);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+        {
+            e[a] = d[a] / r;
+            face += (acc[a] - (wall_acc ? wall_acc[int64_t(j) * D + a] : R(0))) * (-e[a]);
+        }
+        const R p_wall = pi + rhoi * r * fmax(R(0), face);
+        ckMatVec<D, R>(Bi, e, Be);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            fs[a] -= (pi + p_wall) * Be[a] * dWV;
+        diss += (pi - p_wall) * rs.inv_rho0c0 * dWV;
+    }
+    const R Vi = Vol[i];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        force[i * D + a] += fs[a] * Vi;
+    crate[i] += diss * comp[i];
+}
+template <int D, class R>
+__global__ void __launch_bounds__(256) k_ck_first_update(int64_t i0, int64_t n, R dt, const R *__restrict__ mass, const R *__restrict__ fprior,
+                                                         const R *__restrict__ force, R *__restrict__ vel)
+{
+    const int64_t i = i0 + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    const R m = mass[i];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        vel[i * D + a] += (fprior[i * D + a] + force[i * D + a]) / m * dt;
+}
+template <int D, class R>
+__global__ void __launch_bounds__(128)
+    k_ck_second_inner(int64_t i0, int64_t n, R dt, const typename Real4<R>::type *__restrict__ xV, CkList in, TabKernelP<R> k, CkRiemann<D, R> rs,
+                      const R *__restrict__ vel, const R *__restrict__ B, const R *__restrict__ Vol, const R *__restrict__ comp,
+                      R *__restrict__ crate, R *__restrict__ force, R *__restrict__ dpos)
+{
+    CK_INDEX();
+    R vi[D], Bi[D * D];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+    {
+        vi[a] = vel[i * D + a];
+        dpos[i * D + a] += vi[a] * dt * R(0.5); // InitializeKernel
+    }
+#pragma unroll
+    for (int q = 0; q < D * D; ++q)
+        Bi[q] = B[i * D * D + q];
+    R div = R(0), pd[D] = {};
+    const u32 cnt = in.count[i];
+    const u32 *lst = listBase(in.list, in.slice_off, i);
+    for (u32 m = 0; m < cnt; ++m)
+    {
+        const u32 j = listEntry(lst, m);
+        R d[D], Vj, e[D], Be[D];
+        const R r = ckDisp<D, R>(xi, xV, j, d, Vj);
+        const R dWV = tabdW<D, R>(k, r) * Vj;
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            e[a] = d[a] / r;
+        ckMatVec<D, R>(Bi, e, Be);
+        R dvBe = R(0), u = R(0);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+        {
+            const R vj = vel[int64_t(j) * D + a];
+            const R vave = R(0.5) * (vi[a] + vj);
+            dvBe += R(2.0) * (vi[a] - vave) * Be[a];
+            u += (vi[a] - vj) * e[a];
+        }
+        div += dvBe * dWV;
+        const R pj = ckPJump<R>(rs.rho0c0, rs.inv_c0, u) * dWV;
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            pd[a] += pj * e[a];
+    }
+    crate[i] += div * comp[i];
+    const R Vi = Vol[i];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        force[i * D + a] = pd[a] * Vi;
+}
+template <int D, class R>
+__global__ void __launch_bounds__(128)
+    k_ck_second_wall(int64_t i0, int64_t n, const typename Real4<R>::type *__restrict__ xV, const typename Real4<R>::type *__restrict__ xV_t,
+                     CkList in, TabKernelP<R> k, CkRiemann<D, R> rs, const R *__restrict__ vel, const R *__restrict__ wall_vel,
+                     const R *__restrict__ wall_n, const R *__restrict__ B, const R *__restrict__ Vol, const R *__restrict__ comp,
+                     R *__restrict__ crate, R *__restrict__ force)
+{
+    CK_INDEX();
+    const u32 cnt = in.count[i];
+    if (cnt == 0)
+        return;
+    R vi[D], Bi[D * D];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        vi[a] = vel[i * D + a];
+#pragma unroll
+    for (int q = 0; q < D * D; ++q)
+        Bi[q] = B[i * D * D + q];
+    R div = R(0), pd[D] = {};
+    const u32 *lst = listBase(in.list, in.slice_off, i);
+    for (u32 m = 0; m < cnt; ++m)
+    {
+        const u32 j = listEntry(lst, m);
+        R d[D], Vj, e[D], Be[D], vd[D], nj[D];
+        const R r = ckDisp<D, R>(xi, xV_t, j, d, Vj);
+        const R dWV = tabdW<D, R>(k, r) * Vj;
+        R en = R(0);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+        {
+            e[a] = d[a] / r;
+            nj[a] = wall_n[int64_t(j) * D + a];
+            vd[a] = R(2.0) * (vi[a] - (wall_vel ? wall_vel[int64_t(j) * D + a] : R(0)));
+            en += e[a] * nj[a];
+        }
+        ckMatVec<D, R>(Bi, e, Be);
+        const R sgn = en > R(0) ? R(1) : (en < R(0) ? R(-1) : R(0));
+        R dvBe = R(0), u = R(0);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+        {
+            dvBe += vd[a] * Be[a];
+            u += vd[a] * (sgn * nj[a]);
+        }
+        div += dvBe * dWV;
+        const R pj = ckPJump<R>(rs.rho0c0, rs.inv_c0, u) * dWV;
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            pd[a] += pj * (sgn * nj[a]);
+    }
+    crate[i] += div * comp[i];
+    const R Vi = Vol[i];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        force[i * D + a] += pd[a] * Vi;
+}
+template <class R>
+__global__ void __launch_bounds__(256)
+    k_ck_second_update(int64_t i0, int64_t n, R dt, R rho0, R *__restrict__ comp, const R *__restrict__ crate, R *__restrict__ rho)
+{
+    const int64_t i = i0 + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+    const R c = comp[i] + R(0.5) * dt * crate[i];
+    comp[i] = c;
+    rho[i] = c * rho0;
+}
+
 static sphb200_status ckCheck(sphb200_relation *r, bool want_inner, const char *who)
 {
     sphb200_ctx *ctx = r->ctx;
@@ -378,10 +691,213 @@ static sphb200_status ckSurfaceIndication(sphb200_relation *inner, sphb200_relat
                                    ctx->stream));
     return SPHB200_OK;
 }
+
+template <int D, class R>
+static CkRiemann<D, R> ckRiemannOf(sphb200_body *b)
+{
+    // riemann_solver.h:62-70 with rho0c0_i = rho0c0_j
+    const R a = R(b->rho0) * R(b->c0), c = a;
+    CkRiemann<D, R> rs;
+    rs.inv_rho0c0 = (a + c) / (a * a + c * c);
+    rs.rho0c0 = R(2.0) * a * c * (R(1.0) / (a + c));
+    rs.inv_c0 = R(0.5) * (R(b->rho0) + R(b->rho0)) * rs.inv_rho0c0;
+    return rs;
+}
+#define CK_FLAT(b) gridFor((b)->own_end - (b)->own_begin, 256), 256, 0, ctx->stream
+
+// registerStateVariable<Real>("Compression", Real(1)): one, not zero, when first registered
+template <class R>
+static sphb200_status compressionVar(sphb200_body *b, R **out)
+{
+    sphb200_ctx *ctx = b->ctx;
+    const bool fresh = b->find("Compression") == nullptr;
+    SPHB_TRY(getVarPtr<R>(b, "Compression", 1, out, true));
+    if (fresh && b->n > 0)
+    {
+        k_ck_fill<R><<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(b->n, R(1), *out);
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status ckAdvectionStepSetup(sphb200_body *b)
+{
+    sphb200_ctx *ctx = b->ctx;
+    if (b->own_end <= b->own_begin)
+        return SPHB200_OK;
+    R *mass, *rho, *vol, *dpos;
+    SPHB_TRY(getVarPtr<R>(b, "Mass", 1, &mass, true));
+    SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
+    SPHB_TRY(getVarPtr<R>(b, "VolumetricMeasure", 1, &vol, true));
+    SPHB_TRY(getVarPtr<R>(b, "Displacement", D, &dpos, true));
+    k_ck_setup<D, R><<<CK_FLAT(b)>>>(b->own_begin, b->own_end, mass, rho, vol, dpos);
+    SPHB_LAUNCH_CHECK(ctx);
+    b->xV_vol_dirty = true; // the neighbours' Vol_j is read from the packed xV
+    return SPHB200_OK;
+}
+template <int D, class R>
+static sphb200_status ckUpdateParticlePosition(sphb200_body *b)
+{
+    sphb200_ctx *ctx = b->ctx;
+    if (b->own_end <= b->own_begin)
+        return SPHB200_OK;
+    R *pos, *dpos;
+    SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos, true));
+    SPHB_TRY(getVarPtr<R>(b, "Displacement", D, &dpos, true));
+    k_ck_axpy<R><<<gridFor((b->own_end - b->own_begin) * D, 256), 256, 0, ctx->stream>>>(b->own_begin * D, b->own_end * D, pos, dpos);
+    SPHB_LAUNCH_CHECK(ctx);
+    b->rec_b_valid = false;
+    return SPHB200_OK;
+}
+template <int D, class R>
+static sphb200_status ckTimeStep(sphb200_body *b, int kind, double speed_ref, double cfl, double *out)
+{
+    sphb200_ctx *ctx = b->ctx;
+    BodyP<D, R> &P = b->P<D, R>();
+    R *vel, *force, *fprior, *mass;
+    SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel, true));
+    SPHB_TRY(getVarPtr<R>(b, "Force", D, &force, true));
+    SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
+    SPHB_TRY(getVarPtr<R>(b, "Mass", 1, &mass, true));
+    SPHB_TRY(reduceReset(ctx, kind, false));
+    if (b->own_end > b->own_begin)
+    {
+        k_ck_dt_max<D, R><<<148 * 4, 256, 0, ctx->stream>>>(b->own_begin, b->own_end, kind, R(b->c0), P.h, vel, force, fprior, mass,
+                                                           static_cast<unsigned long long *>(ctx->reduce_dev.p) + kind);
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    double m;
+    SPHB_TRY(reduceRead(ctx, kind, &m));
+    if (kind == 0) // fluid_time_step_ck.hpp:31-35
+        *out = double(R(cfl) * P.h / (R(m) + Tiny<R>::value));
+    else // fluid_time_step_ck.cpp:23-25
+        *out = double(R(cfl) * P.h / (std::max(std::sqrt(R(m)), R(speed_ref)) + Tiny<R>::value));
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status ckAcousticHalf(sphb200_relation *inner, sphb200_relation *wall, double dt_, int second)
+{
+    sphb200_ctx *ctx = inner->ctx;
+    sphb200_body *b = inner->body;
+    const char *who = second ? "ck_acoustic_step_2nd_half" : "ck_acoustic_step_1st_half";
+    SPHB_TRY(ckCheck(inner, true, who));
+    if (wall)
+        SPHB_TRY(ckCheck(wall, false, who));
+    if (b->own_end <= b->own_begin)
+        return SPHB200_OK;
+    if (!b->find("LinearCorrectionMatrix"))
+        return ctx->fail(SPHB200_ERR_NOT_FOUND, std::string(who) + ": LinearCorrectionMatrix has not been computed (ck_linear_correction_matrix)");
+    SPHB_TRY((ensurePacked<D, R>(b)));
+    R *rho, *mass, *p, *comp, *crate, *vel, *dpos, *force, *fprior, *B, *vol;
+    SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
+    SPHB_TRY(getVarPtr<R>(b, "Mass", 1, &mass, true));
+    SPHB_TRY(getVarPtr<R>(b, "Pressure", 1, &p, true));
+    SPHB_TRY(compressionVar<R>(b, &comp));
+    SPHB_TRY(getVarPtr<R>(b, "CompressionRate", 1, &crate, true));
+    SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel, true));
+    SPHB_TRY(getVarPtr<R>(b, "Displacement", D, &dpos, true));
+    SPHB_TRY(getVarPtr<R>(b, "Force", D, &force, true));
+    SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
+    SPHB_TRY(getVarPtr<R>(b, "LinearCorrectionMatrix", D * D, &B));
+    SPHB_TRY(getVarPtr<R>(b, "VolumetricMeasure", 1, &vol, true));
+    SPHB_TRY(ensureList(inner, 0));
+    const R h = b->P<D, R>().h, dt = R(dt_);
+    const CkRiemann<D, R> rs = ckRiemannOf<D, R>(b);
+    auto *xV = static_cast<const typename Real4<R>::type *>(b->xV.p);
+    const int64_t i0 = b->own_begin, i1 = b->own_end;
+    if (!second)
+    {
+        k_ck_first_init<D, R><<<CK_FLAT(b)>>>(i0, i1, dt, R(b->rho0), R(b->c0), comp, crate, rho, p, vel, dpos);
+        SPHB_LAUNCH_CHECK(ctx);
+        k_ck_first_inner<D, R><<<CK_GRID(b)>>>(i0, i1, xV, ckListOf(inner->lists[0]), makeTabKernel<D, R>(h, h), rs, p, B, vol, comp, crate, force);
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    else
+    {
+        k_ck_second_inner<D, R><<<CK_GRID(b)>>>(i0, i1, dt, xV, ckListOf(inner->lists[0]), makeTabKernel<D, R>(h, h), rs, vel, B, vol, comp, crate,
+                                                force, dpos);
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    for (size_t t = 0; wall && t < wall->targets.size(); ++t)
+    {
+        sphb200_body *tb = wall->targets[t];
+        SPHB_TRY((ensurePacked<D, R>(tb)));
+        SPHB_TRY(ensureList(wall, t));
+        auto *xVt = static_cast<const typename Real4<R>::type *>(tb->xV.p);
+        const TabKernelP<R> kc = makeTabKernel<D, R>(h, tb->P<D, R>().h);
+        R *w_acc = nullptr, *w_vel = nullptr, *w_n = nullptr;
+        if (tb->find("Acceleration"))
+            SPHB_TRY(getVarPtr<R>(tb, "Acceleration", D, &w_acc));
+        if (tb->find("Velocity"))
+            SPHB_TRY(getVarPtr<R>(tb, "Velocity", D, &w_vel));
+        if (!second)
+            k_ck_first_wall<D, R><<<CK_GRID(b)>>>(i0, i1, xV, xVt, ckListOf(wall->lists[t]), kc, rs, p, rho, mass, fprior, w_acc, B, vol, comp, crate, force);
+        else
+        {
+            if (!tb->find("NormalDirection"))
+                return ctx->fail(SPHB200_ERR_NOT_FOUND, std::string(who) + ": wall body has no NormalDirection");
+            SPHB_TRY(getVarPtr<R>(tb, "NormalDirection", D, &w_n));
+            k_ck_second_wall<D, R><<<CK_GRID(b)>>>(i0, i1, xV, xVt, ckListOf(wall->lists[t]), kc, rs, vel, w_vel, w_n, B, vol, comp, crate, force);
+        }
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    if (!second)
+        k_ck_first_update<D, R><<<CK_FLAT(b)>>>(i0, i1, dt, mass, fprior, force, vel);
+    else
+        k_ck_second_update<R><<<CK_FLAT(b)>>>(i0, i1, dt, R(b->rho0), comp, crate, rho);
+    SPHB_LAUNCH_CHECK(ctx);
+    b->rec_b_valid = false;
+    b->acoustic_max_valid = false;
+    return SPHB200_OK;
+}
 } // namespace sphb
 
 extern "C"
 {
+sphb200_status sphb200_ck_advection_step_setup(sphb200_body *b)
+{
+    if (!b)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, ckAdvectionStepSetup, b);
+}
+sphb200_status sphb200_ck_update_particle_position(sphb200_body *b)
+{
+    if (!b)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, ckUpdateParticlePosition, b);
+}
+sphb200_status sphb200_ck_acoustic_dt(sphb200_body *b, double cfl, double *dt_out)
+{
+    if (!b || !dt_out)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, ckTimeStep, b, 0, 0.0, cfl, dt_out);
+}
+sphb200_status sphb200_ck_advection_dt(sphb200_body *b, double U_ref, double cfl, double *dt_out)
+{
+    if (!b || !dt_out)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, ckTimeStep, b, 1, U_ref, cfl, dt_out);
+}
+sphb200_status sphb200_ck_acoustic_step_1st_half(sphb200_relation *inner, sphb200_relation *wall, double dt)
+{
+    if (!inner || (wall && wall->ctx != inner->ctx))
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(inner->ctx->device);
+    return SPHB_DISPATCH(inner->ctx, ckAcousticHalf, inner, wall, dt, 0);
+}
+sphb200_status sphb200_ck_acoustic_step_2nd_half(sphb200_relation *inner, sphb200_relation *wall, double dt)
+{
+    if (!inner || (wall && wall->ctx != inner->ctx))
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(inner->ctx->device);
+    return SPHB_DISPATCH(inner->ctx, ckAcousticHalf, inner, wall, dt, 1);
+}
 sphb200_status sphb200_ck_density_regularization(sphb200_relation *inner, sphb200_relation *contact, int free_surface)
 {
     if (!inner || (contact && contact->ctx != inner->ctx))

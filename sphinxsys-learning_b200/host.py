@@ -235,6 +235,28 @@ class SPHSystem:
     def ck_free_surface_indication(self, inner, contact=None):
         self.check(self.lib.sphb200_ck_free_surface_indication(inner.h, contact.h if contact else None))
 
+    def ck_advection_step_setup(self, body):
+        self.check(self.lib.sphb200_ck_advection_step_setup(body.h))
+
+    def ck_update_particle_position(self, body):
+        self.check(self.lib.sphb200_ck_update_particle_position(body.h))
+
+    def ck_acoustic_dt(self, body, cfl=0.6):
+        out = C.c_double()
+        self.check(self.lib.sphb200_ck_acoustic_dt(body.h, cfl, C.byref(out)))
+        return out.value
+
+    def ck_advection_dt(self, body, U_ref, cfl=0.25):
+        out = C.c_double()
+        self.check(self.lib.sphb200_ck_advection_dt(body.h, U_ref, cfl, C.byref(out)))
+        return out.value
+
+    def ck_acoustic_1st_half(self, inner, wall=None, dt=0.0):
+        self.check(self.lib.sphb200_ck_acoustic_step_1st_half(inner.h, wall.h if wall else None, dt))
+
+    def ck_acoustic_2nd_half(self, inner, wall=None, dt=0.0):
+        self.check(self.lib.sphb200_ck_acoustic_step_2nd_half(inner.h, wall.h if wall else None, dt))
+
     def total_kinetic_energy(self, body):
         out = C.c_double()
         self.check(self.lib.sphb200_total_kinetic_energy(body.h, C.byref(out)))

@@ -176,3 +176,43 @@ def test_reference_dtw_restatement_known_answers():
     assert vg.dtw_reference(a, np.arange(20.0)) == float("inf")  # length changed by > 20 %: the reference exits
     v = np.stack([a, a], 1)
     assert vg.dtw_reference(v, v) == 0.0
+
+
+def test_ck_acoustic_oracle_agrees_with_an_independent_restatement(pk, oracle):
+    """row f3: the C++ oracle of the CK dam break (oracle/oracle_ck.hpp: corrected acoustic steps on Compression /
+    Displacement, tabulated kernel, LinearCorrectionMatrix(0.5), interval-triggered advection steps) against the numpy
+    restatement that was written first and independently (oracle/experiments/dambreak2d_ck.py: k-d tree neighbours,
+    vectorised pair sums): 200 acoustic steps = 40 advection steps of the 2-D main, every dt equal, fields to 1e-10"""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "experiments"))
+    import dambreak2d_ck as nk
+    dp = 0.05
+    o = pk.cases.DamBreakCK(oracle, ndim=2, dp=dp, real_bytes=8, with_observer=False)
+    m = nk.DamBreak2DCK(dp=dp)
+    interval, present, adv = m.advection_dt(), 0.0, 0
+    for it in range(200):
+        dt = m.acoustic_dt()
+        m.time += dt
+        present += dt
+        m.first_half(dt)
+        m.second_half(dt)
+        did = o.acoustic_step_2d()
+        assert abs(o.dt - dt) <= 1e-12 * dt, (it, o.dt, dt)
+        assert did == (present > interval)
+        if did:
+            present, interval = 0.0, m.advection_dt()
+            adv += 1
+            m.x = m.x + m.dpos
+            m.relations()
+            m.density_regularization()
+            m.advection_setup()
+            m.correction_matrix()
+    assert adv >= 30
+    n = len(m.x)
+    for name, ref in (("Position", m.x), ("Velocity", m.v), ("Density", m.rho), ("Compression", m.comp), ("CompressionRate", m.crate),
+                      ("Force", m.F), ("LinearCorrectionMatrix", m.B.reshape(n, -1))):
+        got = pk.cases.by_original_id(o.water, o.water.get(name)).reshape(n, -1)
+        ref = np.asarray(ref).reshape(n, -1)
+        err = np.linalg.norm(got - ref) / max(np.linalg.norm(ref), 1e-300)
+        assert err < 1e-10, (name, err)
+    assert abs(o.mechanical_energy() - m.energy()) < 1e-12

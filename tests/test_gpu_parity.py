@@ -155,6 +155,53 @@ def test_ck_flavour_dynamics(pk, gpu, oracle, ndim, dp, real_bytes):
     assert out["gpu"]["Compression"].min() >= 1.0 and out["gpu"]["DensityInternal"].min() < 1.0
 
 
+CK_FIELDS = ("Position", "Velocity", "Density", "Pressure", "Compression", "CompressionRate", "Force", "Displacement",
+             "VolumetricMeasure", "LinearCorrectionMatrix")
+
+
+@pytest.mark.parametrize("real_bytes", [8, 4])
+def test_ck_dambreak_3d_advection_steps(pk, gpu, oracle, real_bytes):
+    """row f3: whole outer iterations of tests_sycl/3d_examples/test_3d_dambreak_sycl/dambreak.cpp:187-222 - density
+    regularisation, advection-step set-up, spatial-temporal surface indication, correction matrix, the corrected
+    acoustic sub-steps with the wall, position update, re-configuration - on the CUDA library against the oracle:
+    Dt and every acoustic dt to 1e-12 in fp64, fields within the north-star tolerance"""
+    g, o = both(pk, gpu, oracle, pk.cases.DamBreakCK, ndim=3, dp=0.05, real_bytes=real_bytes, with_observer=False)
+    for c in (g, o):   # a state with pressure, velocity and a deformed lattice from the first sub-step on
+        jitter(c.water, 0.15)
+        set_field(c.water, "Velocity", seeded_state(c, seed=7)["Velocity"])
+        c.water.update_cell_list()
+        c.update_configuration(observer=False)
+    tol = FP_TOL[real_bytes]
+    for step in range(3):
+        rg, ro = g.advection_step(observer=False), o.advection_step(observer=False)
+        dt_tol = 1e-12 if real_bytes == 8 else 1e-5     # the reductions are exact, their input fields agree to rounding
+        assert rg[1] == ro[1] and abs(rg[0] - ro[0]) <= dt_tol * ro[0], (step, rg, ro)
+        assert abs(g.dt - o.dt) <= dt_tol * o.dt
+        for nm in CK_FIELDS:
+            a, b = field(g.water, nm), field(o.water, nm)
+            assert rel_l2(a, b) < tol * (10 if nm in ("CompressionRate", "Force") and real_bytes == 4 else 1), (step, nm, rel_l2(a, b))
+    assert g.n_acoustic == o.n_acoustic >= 6
+    assert np.abs(field(g.water, "Velocity")).max() > 0.1
+
+
+@pytest.mark.parametrize("real_bytes", [8, 4])
+def test_ck_dambreak_2d_single_loop(pk, gpu, oracle, real_bytes):
+    """the 2-D twin's single loop (dambreak_sycl.cpp:176-228): acoustic steps with an interval-triggered advection step"""
+    g, o = both(pk, gpu, oracle, pk.cases.DamBreakCK, ndim=2, dp=0.025, real_bytes=real_bytes, with_observer=False)
+    n_adv = 0
+    for it in range(60):
+        dg, do = g.acoustic_step_2d(), o.acoustic_step_2d()
+        assert dg == do, it
+        assert abs(g.dt - o.dt) <= (1e-12 if real_bytes == 8 else 1e-5) * o.dt, (it, g.dt, o.dt)
+        n_adv += int(dg)
+    assert n_adv >= 8
+    tol = FP_TOL[real_bytes]
+    for nm in CK_FIELDS:
+        a, b = field(g.water, nm), field(o.water, nm)
+        assert rel_l2(a, b) < tol * (10 if real_bytes == 4 else 1), (nm, rel_l2(a, b))
+    assert abs(g.mechanical_energy() - o.mechanical_energy()) < (1e-9 if real_bytes == 8 else 1e-4)
+
+
 @pytest.mark.parametrize("real_bytes", [8, 4])
 def test_solid_contact_neighbor_builders(pk, gpu, oracle, real_bytes):
     """row f4: NeighborBuilderSelfContact (neighborhood.cpp:123-142: r < rc and r0 > rc on InitialPosition, over a body
