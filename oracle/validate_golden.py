@@ -133,6 +133,50 @@ def dambreak_3d(n_samples=3, backend=None, real_bytes=8):
     return out
 
 
+def dambreak_3d_ck(n_samples=3, backend=None, real_bytes=8):
+    """tests/tests_sycl/3d_examples/test_3d_dambreak_sycl/dambreak.cpp:176-231 (the CK scheme): energy at t = 0, 1, 2, ...,
+    the six probe pressures after every advection step (after the relation update of the observer)"""
+    g = golden("dambreak_3d_ck")
+    c = pk.cases.DamBreakCK(backend or _oracle(), ndim=3, dp=0.05, real_bytes=real_bytes)
+    energy, probe = [c.mechanical_energy()], [c.probe_pressure().copy()]
+    while len(energy) < n_samples and c.time < 20.0:
+        integ = 0.0
+        while integ < 1.0:
+            t0 = c.time
+            c.advection_step()
+            integ += c.time - t0
+            probe.append(c.probe_pressure().copy())
+        energy.append(c.mechanical_energy())
+    out = {"case": "dambreak_3d_ck", "advection_steps": c.n_advection,
+           "WaterBody_TotalMechanicalEnergy": compare(g["WaterBody_TotalMechanicalEnergy"], [energy])}
+    if n_samples >= 21:
+        out["FluidObserver_Pressure"] = compare(g["FluidObserver_Pressure"], np.asarray(probe).T)
+    out["ours_energy"] = [float(e) for e in energy]
+    return out
+
+
+def dambreak_2d_ck(n_samples=4, backend=None, real_bytes=8):
+    """tests/tests_sycl/2d_examples/test_2d_dambreak_sycl/dambreak_sycl.cpp:168-240: sample 0 at advection_steps = 1, then
+    whenever advection_steps % 200 == 0 (after the position update, before the configuration update)"""
+    g = golden("dambreak_2d_ck")
+    c = pk.cases.DamBreakCK(backend or _oracle(), ndim=2, dp=0.025, real_bytes=real_bytes)
+    energy, probe = [c.mechanical_energy()], [c.probe_pressure().copy()]
+
+    def sample():
+        if c.advection_steps % 200 == 0:
+            energy.append(c.mechanical_energy())
+            c.obs_contact.update()                      # fluid_observer_contact_relation.exec() before the probe is written
+            probe.append(c.probe_pressure().copy())
+
+    while len(energy) < n_samples and c.time < 20.0:
+        c.acoustic_step_2d(on_advection=sample)
+    out = {"case": "dambreak_2d_ck", "advection_steps": c.advection_steps,
+           "WaterBody_TotalMechanicalEnergy": compare(g["WaterBody_TotalMechanicalEnergy"], [energy]),
+           "FluidObserver_Pressure": compare(g["FluidObserver_Pressure"], np.asarray(probe).T)}
+    out["ours_energy"] = [float(e) for e in energy]
+    return out
+
+
 def taylor_green(n_samples=3, backend=None, real_bytes=8):
     """taylor_green.cpp:150-192: kinetic energy at t = 0, 0.1, ...; maximum speed from t = 0.1 on"""
     g = golden("taylor_green_2d")
@@ -179,8 +223,9 @@ def twisting_column(n_samples=200, backend=None, real_bytes=8):
             "MyObserver_Velocity": cmp(g["MyObserver_Velocity"], vel)}
 
 
-ALL = {"dambreak_2d": dambreak_2d, "taylor_green": taylor_green, "twisting_column": twisting_column, "dambreak_3d": dambreak_3d}
-FULL = {"dambreak_2d": 23, "taylor_green": 51, "twisting_column": 3127, "dambreak_3d": 21}
+ALL = {"dambreak_2d": dambreak_2d, "taylor_green": taylor_green, "twisting_column": twisting_column, "dambreak_3d": dambreak_3d,
+       "dambreak_3d_ck": dambreak_3d_ck, "dambreak_2d_ck": dambreak_2d_ck}
+FULL = {"dambreak_2d": 23, "taylor_green": 51, "twisting_column": 3127, "dambreak_3d": 21, "dambreak_3d_ck": 21, "dambreak_2d_ck": 23}
 
 if __name__ == "__main__":
     full = "--full" in sys.argv

@@ -19,6 +19,9 @@ CASES = {
     "dambreak_3d": ("3d_examples/test_3d_dambreak", ["WaterBody_TotalMechanicalEnergy", "FluidObserver_Pressure"]),
     "taylor_green_2d": ("2d_examples/test_2d_taylor_green", ["WaterBody_TotalKineticEnergy", "WaterBody_MaximumSpeed"]),
     "twisting_column_3d": ("3d_examples/test_3d_twisting_column", ["MyObserver_Position", "MyObserver_Velocity"]),
+    # the CK / SYCL twins
+    "dambreak_3d_ck": ("tests_sycl/3d_examples/test_3d_dambreak_sycl", ["WaterBody_TotalMechanicalEnergy", "FluidObserver_Pressure"]),
+    "dambreak_2d_ck": ("tests_sycl/2d_examples/test_2d_dambreak_sycl", ["WaterBody_TotalMechanicalEnergy", "FluidObserver_Pressure"]),
 }
 
 
