@@ -720,7 +720,28 @@ def test_run_level_observables_against_the_reference_fixtures(pk, gpu):
     assert r["WaterBody_TotalMechanicalEnergy"]["first_sample_over_1pct"] >= 5, r
     r = vg.taylor_green(51, backend=gpu)
     assert r["WaterBody_TotalKineticEnergy"]["dtw_ok"] and r["WaterBody_MaximumSpeed"]["dtw_ok"], r
-    assert r["WaterBody_TotalKineticEnergy"]["first_sample_over_1pct"] >= 2, r@pytest.mark.gpu
+    assert r["WaterBody_TotalKineticEnergy"]["first_sample_over_1pct"] >= 2, r
+
+
+@pytest.mark.gpu
+def test_ck_run_level_observables_against_the_sycl_fixtures(pk, gpu):
+    """the CK scheme on the device over the FULL stored series of the SYCL twins' fixtures (tests/golden/dambreak_{2d,3d}_ck.json,
+    from tests/tests_sycl/{2d,3d}_examples/test_{2d,3d}_dambreak_sycl/regression_test_tool): the reference's own acceptance test
+    (DTW <= 1.01 x stored) passes for the energy and every probe; strictly the stored runs are 5 % (3-D) / 8 % (2-D) away
+    after the impact - they start with a smaller lattice over-compression than today's CompressionSummation gives
+    (t = 1: stored 0.50059, today's scheme 0.50683), i.e. they too predate the current sources"""
+    from oracle import validate_golden as vg
+    r = vg.dambreak_3d_ck(21, backend=gpu)
+    e = r["WaterBody_TotalMechanicalEnergy"]
+    assert e["snapshots"] == [21, 21] and e["dtw_ok"] and e["max_rel_dev"] < 0.08, r
+    assert r["FluidObserver_Pressure"]["dtw_ok"], r
+    assert abs(r["ours_energy"][1] - 0.5068257378046827) < 2e-4, r["ours_energy"][:3]      # the oracle's value at t = 1
+    r = vg.dambreak_2d_ck(23, backend=gpu)
+    assert r["WaterBody_TotalMechanicalEnergy"]["dtw_ok"] and r["FluidObserver_Pressure"]["dtw_ok"], r
+    assert abs(r["ours_energy"][1] - 1.0083686730710035) < 2e-4, r["ours_energy"][:3]
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("ndim,dp,real_bytes,amp", [(3, 0.05, 8, 0.0), (3, 0.05, 8, 0.3), (3, 0.05, 4, 0.3), (2, 0.025, 8, 0.3)])
 def test_lanes_per_group_variants_of_the_second_half_agree(pk, gpu, oracle, ndim, dp, real_bytes, amp):
     """k_second_half_quad (2 or 4 lanes split a group's union list, partial sums reduced by shuffles) against
