@@ -272,6 +272,19 @@ sphb200_status sphb200_solid_dt(sphb200_body *b, double cfl, double *dt_out);
  * returns the total like the reference's overload. */
 sphb200_status sphb200_exclusive_scan_u32(sphb200_ctx *ctx, const uint32_t *in, uint32_t *out, int64_t n, uint64_t *total);
 
+/* The same scan for callers that cannot allocate.  It has NO counterpart in the reference and was added
+ * (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  DEVICE pointers:
+ * d_in holds n uint32, d_out n + 1 (d_out[i] = sum of d_in[0..i), d_out[n] = the total; in place, d_out == d_in, is not
+ * supported); enqueued on the context's stream, no host synchronisation.  The call performs no cudaMalloc / cudaFree
+ * and calls no allocating library routine: the scan's scratch (one partial sum per tile of 4096 elements) is a
+ * file-scope device array of 16 384 tiles, so n <= 67 108 864 - larger n returns SPHB200_ERR_INVALID with a message
+ * naming the limit.  Every GPU that loads the library holds those 64 KB until exit.  All calls on a device share the
+ * array: calls that overlap on the GPU (two contexts or streams on one device) race, callers must order them.  Nothing
+ * in it has to start at zero (every word is written before it is read), so back-to-back calls need no clearing.  The
+ * first call per device resolves the array's device address (cudaGetSymbolAddress); do one call (n = 0 will do)
+ * before starting a graph capture. */
+sphb200_status sphb200_exclusive_scan_u32_static(sphb200_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n);
+
 /* ---- slab decomposition helpers (multi-GPU; no reference equivalent) ------------ */
 /* enqueue all further work of this context on the caller's cudaStream_t (e.g. torch's current
  * stream, so that torch.distributed collectives and these kernels are ordered without host syncs) */

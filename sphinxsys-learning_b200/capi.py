@@ -111,6 +111,7 @@ SIGNATURES = {
     "sphb200_solid_constrain": (_i, [_vp, _i64p, _i64]),
     "sphb200_solid_dt": (_i, [_vp, _d, _dp]),
     "sphb200_exclusive_scan_u32": (_i, [_vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), _i64, C.POINTER(C.c_uint64)]),
+    "sphb200_exclusive_scan_u32_static": (_i, [_vp, _vp, _vp, _i64]),
     "sphb200_ctx_set_stream": (_i, [_vp, _vp]),
     "sphb200_body_resize": (_i, [_vp, _i64]),
     "sphb200_body_set_owned_pages": (_i, [_vp, _i, _i]),

@@ -15,6 +15,8 @@
 // hit consecutive sectors.  The frozen position snapshot + Vol is packed into one aligned Real4 record
 // per particle (xV) so a neighbour costs one 16/32-byte load.
 #include "internal.cuh"
+#include <mutex>
+#include <string>
 
 using namespace sphb;
 
@@ -630,6 +632,72 @@ sphb200_status sphb200_exclusive_scan_u32(sphb200_ctx *ctx, const uint32_t *in, 
         memcpy(out, tmp.data(), size_t(n) * 4);
     if (total)
         *total = tmp[size_t(n)];
+    return SPHB200_OK;
+}
+} // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Exclusive scan that allocates nothing (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that
+// forbid it).  Same three kernels as exclusiveScanU32; the tile sums - the scan's only scratch - live in a
+// file-scope device array instead of ctx->scan_tmp.  Every GPU that loads the library holds these 64 KB + 256 B
+// until exit.  In host code `g_scan_static` is a host-side stand-in, not a device address: the address the
+// kernels get is resolved once per device by cudaGetSymbolAddress with that device current.
+// ---------------------------------------------------------------------------------------------
+namespace sphb
+{
+constexpr int64_t kScanStaticTiles = 16384;                        // x kScanTile (4096) = 67 108 864 elements
+constexpr int64_t kScanStaticMaxN = kScanStaticTiles * kScanTile;
+static __device__ __align__(256) u32 g_scan_static[kScanStaticTiles + 64]; // tile sums [0, n_tiles), total at [n_tiles]
+constexpr int kScanStaticMaxDevices = 64;
+static u32 *g_scan_static_ptr[kScanStaticMaxDevices] = {};
+static std::mutex g_scan_static_mutex;
+
+static sphb200_status scanStaticScratch(sphb200_ctx *ctx, u32 **out)
+{
+    if (ctx->device < 0 || ctx->device >= kScanStaticMaxDevices)
+        return ctx->fail(SPHB200_ERR_INVALID, "exclusive_scan_u32_static: device ordinal out of range");
+    std::lock_guard<std::mutex> lock(g_scan_static_mutex);
+    if (!g_scan_static_ptr[ctx->device])
+    {
+        void *p = nullptr;
+        SPHB_CUDA(ctx, cudaSetDevice(ctx->device)); // the address is per device: resolve it with that device current
+        SPHB_CUDA(ctx, cudaGetSymbolAddress(&p, g_scan_static));
+        if (!p)
+            return ctx->fail(SPHB200_ERR_CUDA, "exclusive_scan_u32_static: cudaGetSymbolAddress returned a null address");
+        g_scan_static_ptr[ctx->device] = static_cast<u32 *>(p);
+    }
+    *out = g_scan_static_ptr[ctx->device];
+    return SPHB200_OK;
+}
+} // namespace sphb
+
+extern "C"
+{
+sphb200_status sphb200_exclusive_scan_u32_static(sphb200_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n)
+{
+    if (!ctx || n < 0 || !d_out || (n > 0 && !d_in))
+        return SPHB200_ERR_INVALID;
+    if (n > kScanStaticMaxN)
+        return ctx->fail(SPHB200_ERR_INVALID, "exclusive_scan_u32_static: n = " + std::to_string(n) + " exceeds the static scratch (maximum " +
+                                                  std::to_string(kScanStaticMaxN) + " elements); use sphb200_exclusive_scan_u32");
+    cudaSetDevice(ctx->device);
+    u32 *ts = nullptr;
+    SPHB_TRY(scanStaticScratch(ctx, &ts));
+    if (n == 0)
+    { // total of nothing; also the way to resolve the scratch address ahead of a graph capture
+        SPHB_CUDA(ctx, cudaMemsetAsync(d_out, 0, 4, ctx->stream));
+        return SPHB200_OK;
+    }
+    // nothing in the scratch has to start at zero: k_scan_tiles writes every tile sum [0, n_tiles) and
+    // k_scan_tile_sums writes [n_tiles] before anything reads them, so the last call's contents are dead
+    const int64_t n_tiles = (n + kScanTile - 1) / kScanTile;
+    k_scan_tiles<<<int(n_tiles), kScanBlock, 0, ctx->stream>>>(d_in, d_out, ts, n);
+    SPHB_LAUNCH_CHECK(ctx);
+    k_scan_tile_sums<<<1, kScanBlock, 0, ctx->stream>>>(ts, n_tiles);
+    SPHB_LAUNCH_CHECK(ctx);
+    k_scan_add<<<gridFor(n, 256), 256, 0, ctx->stream>>>(d_out, ts, n, n_tiles, 1);
+    SPHB_LAUNCH_CHECK(ctx);
     return SPHB200_OK;
 }
 } // extern "C"

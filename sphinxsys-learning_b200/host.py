@@ -119,6 +119,10 @@ class SPHSystem:
             v.size, C.byref(total)))
         return out, int(total.value)
 
+    def exclusive_scan_static(self, d_in_ptr, d_out_ptr, n):
+        """sphb200_exclusive_scan_u32_static: device pointers (n in, n + 1 out), scratch in a static device array, no allocation"""
+        self.check(self.lib.sphb200_exclusive_scan_u32_static(self.h, C.c_void_p(d_in_ptr), C.c_void_p(d_out_ptr), int(n)))
+
     # ---- dynamics (exec) ---------------------------------------------------------------------
     def density_summation(self, inner, contact=None, free_surface=False):
         self.check(self.lib.sphb200_density_summation(inner.h, contact.h if contact else None, int(free_surface)))
