@@ -190,7 +190,7 @@ def slab_main(a, pk, stream, rank, world, local_rank, warmup):
     k_ms = k0.elapsed_time(k1) / reps
     peak, peak_src = peaks()
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_second_half_tile (Integration2ndHalf inner+wall) on rank 0's slab",
+    roofline = {"bound": "hbm", "kernel": ("k_second_half_quad" if R == 8 else "k_second_half_tile") + " (Integration2ndHalf inner+wall) on rank 0's slab",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "peak_source": peak_src, "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg_bytes,
                 "pairs_per_particle": pairs / max(owned, 1)}
@@ -369,7 +369,7 @@ def single_gpu(a, pk, stream, device, warmup, R, with_cpu, short=False):
         k12 = kernel_ms(lambda: S.integration_1st_half(case.inner, case.wall_contact, True, 0.0))
         achieved = alg_bytes / (k3 * 1e-3) / 1e9
         st = case.inner.stats()
-        return {"bound": "hbm", "kernel": "Integration2ndHalf inner+wall, fused init/update (k_second_half_tile; wall sums from k_second_half_wall)",
+        return {"bound": "hbm", "kernel": "Integration2ndHalf inner+wall, fused init/update (" + ("k_second_half_quad: 2 lanes per group" if R == 8 else "k_second_half_tile") + "; wall sums from k_second_half_wall)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "peak_source": peak_src, "kernel_ms": k3, "first_half_ms": k12, "algorithmic_bytes_per_launch": alg_bytes,
                 "pairs_per_particle": (pairs_in + pairs_w) / n_f,
@@ -381,8 +381,8 @@ def single_gpu(a, pk, stream, device, warmup, R, with_cpu, short=False):
         # keyed by kernel name and N - a number from the capture, not from this run
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
             tj = json.load(fh)
-        key = f"k_second_half_tile<3,double,2>@{n_f}"
-        if R == 8 and key in tj:
+        key = f"k_second_half_quad<3,double,2,2>@{n_f}"
+        if R == 8 and key in tj and os.environ.get("SPHB200_QUAD", "2") == "2":
             roofline["traffic"] = tj[key]["dram_bytes_per_launch"]
             roofline["traffic_source"] = "profiles/traffic.json (ncu --set full capture of this kernel at this N, not this run)"
     except Exception:
