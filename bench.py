@@ -244,7 +244,7 @@ def slab_main(a, pk, stream, rank, world, local_rank, warmup):
                "config": {"workload": f"test_3d_dambreak lattice dp=1/{round(1 / dp)}: {n_f} fluid particles over {world} x-slabs "
                                       f"(rank 0: {owned} owned + {w.n - owned} halo fluid, {P.case.wall.n} wall)",
                           "acoustic_substeps": sub, "advection_steps": a.steps, "l2": "inputs larger than L2",
-                          "parallelism": f"{world} slabs along x, NCCL halo records per sub-step + migration per advection step",
+                          "parallelism": f"{world} slabs along x; per sub-step: halo records " + ("pushed into the neighbour GPU's memory by the pack kernel (NVLink peer stores, csrc/peer.cu)" if case.peer_halo else "over NCCL send/recv") + " and a device-side NCCL all-reduce of the dt maximum; per advection step: migration + fresh halo over NCCL, one sort",
                           "page_cuts": [int(c) for c in case.cuts], "build_seconds": round(t_build, 1)},
                "roofline": roofline, "step_roofline_frac": step_frac, "a_step_bytes": a_step,
                "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}

@@ -246,6 +246,16 @@ sphb200_status sphb200_ck_free_surface_indication(sphb200_relation *inner, sphb2
  *   ck_acoustic_step_2nd_half      ...2ndHalf... (acoustic_step_2nd_half.hpp:33-38,53-73,83-89,117-137)
  * wall_or_null: contact relation to Solid walls (their Velocity / Acceleration are the averages the wall model reads,
  * base_material.cpp:57-65; absent = zero; NormalDirection is required by the 2nd half). */
+/* Force of the fluid on a structure.  `contact`: a contact relation whose SOURCE is the solid body and whose
+ * targets are fluid bodies.  InteractionDynamicsCK<..., FSI::PressureForceOnStructure<AcousticStep2ndHalfType>> and
+ * FSI::ViscousForceOnStructure<ViscousForceType> (shared_ck/particle_dynamics/fluid_structure_interaction/
+ * force_on_structure.hpp:113-137 and :61-79), including their WithUpdate step ForcePriorCK::UpdateKernel
+ * (general_dynamics/force_prior_ck.h:55-59: ForcePrior += F - PreviousF).  Results in the solid's
+ * "PressureForceFromFluid" / "ViscousForceFromFluid".  The solid's Velocity / Acceleration are the averages the structure
+ * model reads (absent = zero); NormalDirection is required by the pressure force.  corrected != 0: the fluid's
+ * LinearCorrectionMatrix multiplies e_ij (LinearCorrectionCK), 0: NoKernelCorrectionCK. */
+sphb200_status sphb200_ck_pressure_force_from_fluid(sphb200_relation *contact, int corrected);
+sphb200_status sphb200_ck_viscous_force_from_fluid(sphb200_relation *contact, int corrected);
 sphb200_status sphb200_ck_advection_step_setup(sphb200_body *body);
 sphb200_status sphb200_ck_update_particle_position(sphb200_body *body);
 sphb200_status sphb200_ck_acoustic_dt(sphb200_body *body, double cfl, double *dt_out);

@@ -48,6 +48,7 @@ def load():
         "orc_ck_density_regularization": (None, [vp, i, i, i]), "orc_ck_linear_correction_matrix": (None, [vp, i, i, d]),
         "orc_ck_free_surface_indication": (None, [vp, i, i]), "orc_ck_advection_step_setup": (None, [vp, i]),
         "orc_ck_update_particle_position": (None, [vp, i]), "orc_ck_acoustic_dt": (d, [vp, i, d]), "orc_ck_advection_dt": (d, [vp, i, d, d]),
+        "orc_ck_pressure_force_from_fluid": (None, [vp, i, i]), "orc_ck_viscous_force_from_fluid": (None, [vp, i, i]),
         "orc_ck_acoustic_1st_half": (None, [vp, i, i, d]), "orc_ck_acoustic_2nd_half": (None, [vp, i, i, d]), "orc_maximum_speed": (d, [vp, i]), "orc_position_bound": (None, [vp, i, i, dp]), "orc_observe": (None, [vp, i, cp, i, dp]),
         "orc_correction_matrix": (None, [vp, i]), "orc_solid_1st_half": (None, [vp, i, i, d]),
         "orc_solid_2nd_half": (None, [vp, i, d]), "orc_solid_constrain": (None, [vp, i, lp, l]),
@@ -158,6 +159,12 @@ class SPHSystem:
 
     def ck_acoustic_2nd_half(self, inner, wall=None, dt=0.0):
         self.lib.orc_ck_acoustic_2nd_half(self.h, inner.id, wall.id if wall else -1, dt)
+
+    def ck_pressure_force_from_fluid(self, contact, corrected=True):
+        self.lib.orc_ck_pressure_force_from_fluid(self.h, contact.id, int(corrected))
+
+    def ck_viscous_force_from_fluid(self, contact, corrected=True):
+        self.lib.orc_ck_viscous_force_from_fluid(self.h, contact.id, int(corrected))
 
     def ck_free_surface_indication(self, inner, contact=None):
         self.lib.orc_ck_free_surface_indication(self.h, inner.id, contact.id if contact else -1)

@@ -371,6 +371,14 @@ void orc_ck_acoustic_2nd_half(void *sys, int inner, int wall, double dt)
 {
     DISPATCH(sys, ckAcoustic2ndHalf<D, R>(*S.rels[inner], wall >= 0 ? S.rels[wall].get() : nullptr, R(dt)));
 }
+void orc_ck_pressure_force_from_fluid(void *sys, int contact, int corrected)
+{
+    DISPATCH(sys, ckPressureForceFromFluid<D, R>(*S.rels[contact], corrected != 0));
+}
+void orc_ck_viscous_force_from_fluid(void *sys, int contact, int corrected)
+{
+    DISPATCH(sys, ckViscousForceFromFluid<D, R>(*S.rels[contact], corrected != 0));
+}
 void orc_position_bound(void *sys, int body, int upper, double *out3)
 {
     DISPATCH(sys, positionBound<D, R>(*S.bodies[body], upper != 0, out3));

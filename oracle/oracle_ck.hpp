@@ -503,4 +503,130 @@ void ckAcoustic2ndHalf(Relation<D, R> &inner, Relation<D, R> *wall, R dt)
         rho[i] = comp[i] * rho0;
     }
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Force of the fluid on a structure: the source body of the contact relation is the SOLID, its targets
+// are fluid bodies.   shared_ck/particle_dynamics/fluid_structure_interaction/force_on_structure.hpp:61-79 (viscous),
+// :113-137 (pressure); WithUpdate = ForcePriorCK::UpdateKernel (general_dynamics/force_prior_ck.h:55-59).
+// corrected: contact_correction_(j) is the fluid particle's LinearCorrectionMatrix (LinearCorrectionCK) or 1 (NoKernelCorrectionCK).
+// ---------------------------------------------------------------------------------------------------------------
+template <int D, class R>
+inline void forcePriorUpdate(Body<D, R> &b, const char *force_name)
+{
+    const std::string prev_name = std::string("Previous") + force_name;
+    R *fp = b.v("ForcePrior", D), *cur = b.v(force_name, D), *prev = b.v(prev_name.c_str(), D);
+    for (size_t q = 0; q < b.n * D; ++q)
+    {
+        fp[q] += cur[q] - prev[q];
+        prev[q] = cur[q];
+    }
+}
+
+template <int D, class R>
+void ckPressureForceFromFluid(Relation<D, R> &contact, bool corrected)
+{
+    Body<D, R> &b = *contact.body;
+    const long n = long(b.n);
+    const R *pos = b.v("Position", D), *Vol = b.v("VolumetricMeasure"), *vel_ave = b.v("Velocity", D), *acc_ave = b.v("Acceleration", D),
+            *nrm = b.v("NormalDirection", D);
+    R *force = b.v("PressureForceFromFluid", D);
+    for (long q = 0; q < n * D; ++q)
+        force[q] = R(0);
+    for (size_t t = 0; t < contact.targets.size(); ++t)
+    {
+        Body<D, R> &f = *contact.targets[t];
+        const R *fpos = f.v("Position", D), *fvol = f.v("VolumetricMeasure"), *fvel = f.v("Velocity", D), *frho = f.v("Density"),
+                *fmass = f.v("Mass"), *fp = f.v("Pressure"), *ffp = f.v("ForcePrior", D);
+        const R *fB = corrected ? f.v("LinearCorrectionMatrix", D * D) : nullptr;
+        Riemann<R> rs(R(f.mat.rho0), R(f.mat.c0), true);
+        const TabKernel<D, R> k(b.h, f.h);
+#pragma omp parallel for schedule(static)
+        for (long i = 0; i < n; ++i)
+        {
+            R acc[D] = {};
+            const auto &cn = contact.configs[t][i];
+            for (size_t m = 0; m != cn.current_size; ++m)
+            {
+                const size_t j = cn.j[m];
+                R d[D], e[D], ce[D], nf[D];
+                const R r = dispNorm<D, R>(pos + i * D, fpos + j * D, d);
+                for (int a = 0; a < D; ++a)
+                    e[a] = d[a] / r;
+                if (corrected)
+                    matVec<D, R>(fB + j * D * D, e, ce);
+                else
+                    for (int a = 0; a < D; ++a)
+                        ce[a] = e[a];
+                R face = R(0), cen = R(0);
+                for (int a = 0; a < D; ++a)
+                {
+                    face += (ffp[j * D + a] / fmass[j] - acc_ave[i * D + a]) * e[a];
+                    cen += ce[a] * nrm[i * D + a];
+                }
+                const R p_in_wall = fp[j] + frho[j] * r * std::max(R(0), face);
+                const R sgn = cen < R(0) ? R(-1) : (cen > R(0) ? R(1) : R(0));
+                R u = R(0);
+                for (int a = 0; a < D; ++a)
+                {
+                    nf[a] = -sgn * nrm[i * D + a];
+                    u += R(2.0) * (fvel[j * D + a] - vel_ave[i * D + a]) * nf[a];
+                }
+                const R pj = rs.PJump(u), dWV = k.dW(r) * fvol[j];
+                for (int a = 0; a < D; ++a)
+                    acc[a] -= (pj * nf[a] + (p_in_wall + fp[j]) * ce[a]) * dWV;
+            }
+            for (int a = 0; a < D; ++a)
+                force[i * D + a] += acc[a] * Vol[i];
+        }
+    }
+    forcePriorUpdate<D, R>(b, "PressureForceFromFluid");
+}
+
+template <int D, class R>
+void ckViscousForceFromFluid(Relation<D, R> &contact, bool corrected)
+{
+    Body<D, R> &b = *contact.body;
+    const long n = long(b.n);
+    const R *pos = b.v("Position", D), *Vol = b.v("VolumetricMeasure"), *vel_ave = b.v("Velocity", D);
+    R *force = b.v("ViscousForceFromFluid", D);
+    for (long q = 0; q < n * D; ++q)
+        force[q] = R(0);
+    for (size_t t = 0; t < contact.targets.size(); ++t)
+    {
+        Body<D, R> &f = *contact.targets[t];
+        const R *fpos = f.v("Position", D), *fvol = f.v("VolumetricMeasure"), *fvel = f.v("Velocity", D);
+        const R *fB = corrected ? f.v("LinearCorrectionMatrix", D * D) : nullptr;
+        const R mu = R(f.mat.mu), h_sq = f.h * f.h;
+        const TabKernel<D, R> k(b.h, f.h);
+#pragma omp parallel for schedule(static)
+        for (long i = 0; i < n; ++i)
+        {
+            R acc[D] = {};
+            const auto &cn = contact.configs[t][i];
+            for (size_t m = 0; m != cn.current_size; ++m)
+            {
+                const size_t j = cn.j[m];
+                R d[D], e[D], ce[D];
+                const R r = dispNorm<D, R>(pos + i * D, fpos + j * D, d);
+                for (int a = 0; a < D; ++a)
+                    e[a] = d[a] / r;
+                if (corrected)
+                    matVec<D, R>(fB + j * D * D, e, ce);
+                else
+                    for (int a = 0; a < D; ++a)
+                        ce[a] = e[a];
+                const R denom = sqnorm<D, R>(d) + R(0.01) * h_sq;
+                R rce = R(0);
+                for (int a = 0; a < D; ++a)
+                    rce += d[a] * ce[a];
+                const R w = rce * mu * k.dW(r) * fvol[j];
+                for (int a = 0; a < D; ++a)
+                    acc[a] += w * ((vel_ave[i * D + a] - fvel[j * D + a]) / denom);
+            }
+            for (int a = 0; a < D; ++a)
+                force[i * D + a] += acc[a] * Vol[i];
+        }
+    }
+    forcePriorUpdate<D, R>(b, "ViscousForceFromFluid");
+}
 } // namespace orc

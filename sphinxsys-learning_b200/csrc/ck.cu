@@ -551,6 +551,131 @@ __global__ void __launch_bounds__(256)
     rho[i] = c * rho0;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Force of the fluid on a structure: source of the contact relation = the solid, targets = fluid bodies.
+//   FSI::PressureForceFromFluid<Contact<WithUpdate, ...>>::InteractKernel::interact   force_on_structure.hpp:113-137
+//   FSI::ViscousForceFromFluid<Contact<WithUpdate, ...>>::InteractKernel::interact    force_on_structure.hpp:61-79
+//   WithUpdate = ForcePriorCK::UpdateKernel                                            force_prior_ck.h:55-59
+// B_t: the fluid's LinearCorrectionMatrix (LinearCorrectionCK) or null (NoKernelCorrectionCK: identity).
+// ---------------------------------------------------------------------------------------------------------------
+template <int D, class R>
+__global__ void __launch_bounds__(128)
+    k_ck_fsi_pressure(int64_t i0, int64_t n, int first, const typename Real4<R>::type *__restrict__ xV,
+                      const typename Real4<R>::type *__restrict__ xV_t, CkList in, TabKernelP<R> k, R rho0c0, R inv_c0,
+                      const R *__restrict__ vel_ave, const R *__restrict__ acc_ave, const R *__restrict__ nrm, const R *__restrict__ Vol,
+                      const R *__restrict__ t_vel, const R *__restrict__ t_rho, const R *__restrict__ t_mass, const R *__restrict__ t_p,
+                      const R *__restrict__ t_fprior, const R *__restrict__ B_t, R *__restrict__ force)
+{
+    CK_INDEX();
+    R vi[D], ai[D], ni[D], acc[D] = {};
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+    {
+        vi[a] = vel_ave ? vel_ave[i * D + a] : R(0);
+        ai[a] = acc_ave ? acc_ave[i * D + a] : R(0);
+        ni[a] = nrm[i * D + a];
+    }
+    const u32 cnt = in.count[i];
+    const u32 *lst = listBase(in.list, in.slice_off, i);
+    for (u32 m = 0; m < cnt; ++m)
+    {
+        const u32 j = listEntry(lst, m);
+        R d[D], Vj, e[D], ce[D], nf[D];
+        const R r = ckDisp<D, R>(xi, xV_t, j, d, Vj);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            e[a] = d[a] / r;
+        if (B_t)
+            ckMatVec<D, R>(B_t + int64_t(j) * D * D, e, ce);
+        else
+        {
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+                ce[a] = e[a];
+        }
+        const R mj = t_mass[j], pj = t_p[j];
+        R face = R(0), cen = R(0);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+        {
+            face += (t_fprior[int64_t(j) * D + a] / mj - ai[a]) * e[a];
+            cen += ce[a] * ni[a];
+        }
+        const R p_in_wall = pj + t_rho[j] * r * fmax(R(0), face);
+        const R sgn = cen < R(0) ? R(-1) : (cen > R(0) ? R(1) : R(0));
+        R u = R(0);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+        {
+            nf[a] = -sgn * ni[a];
+            u += R(2.0) * (t_vel[int64_t(j) * D + a] - vi[a]) * nf[a];
+        }
+        const R jump = ckPJump<R>(rho0c0, inv_c0, u), dWV = tabdW<D, R>(k, r) * Vj;
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            acc[a] -= (jump * nf[a] + (p_in_wall + pj) * ce[a]) * dWV;
+    }
+    const R Vi = Vol[i];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        force[i * D + a] = (first ? R(0) : force[i * D + a]) + acc[a] * Vi;
+}
+template <int D, class R>
+__global__ void __launch_bounds__(128)
+    k_ck_fsi_viscous(int64_t i0, int64_t n, int first, const typename Real4<R>::type *__restrict__ xV,
+                     const typename Real4<R>::type *__restrict__ xV_t, CkList in, TabKernelP<R> k, R mu, R h_sq, const R *__restrict__ vel_ave,
+                     const R *__restrict__ Vol, const R *__restrict__ t_vel, const R *__restrict__ B_t, R *__restrict__ force)
+{
+    CK_INDEX();
+    R vi[D], acc[D] = {};
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        vi[a] = vel_ave ? vel_ave[i * D + a] : R(0);
+    const u32 cnt = in.count[i];
+    const u32 *lst = listBase(in.list, in.slice_off, i);
+    for (u32 m = 0; m < cnt; ++m)
+    {
+        const u32 j = listEntry(lst, m);
+        R d[D], Vj, e[D], ce[D];
+        const R r = ckDisp<D, R>(xi, xV_t, j, d, Vj);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            e[a] = d[a] / r;
+        if (B_t)
+            ckMatVec<D, R>(B_t + int64_t(j) * D * D, e, ce);
+        else
+        {
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+                ce[a] = e[a];
+        }
+        const R denom = sqnormExact<D, R>(d) + R(0.01) * h_sq;
+        R rce = R(0);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            rce += d[a] * ce[a];
+        const R w = rce * mu * tabdW<D, R>(k, r) * Vj;
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+            acc[a] += w * ((vi[a] - t_vel[int64_t(j) * D + a]) / denom);
+    }
+    const R Vi = Vol[i];
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+        force[i * D + a] = (first ? R(0) : force[i * D + a]) + acc[a] * Vi;
+}
+template <class R>
+__global__ void __launch_bounds__(256)
+    k_ck_force_prior_update(int64_t e0, int64_t e1, R *__restrict__ fprior, const R *__restrict__ cur, R *__restrict__ prev)
+{
+    const int64_t e = e0 + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (e >= e1)
+        return;
+    const R c = cur[e];
+    fprior[e] += c - prev[e];
+    prev[e] = c;
+}
+
 static sphb200_status ckCheck(sphb200_relation *r, bool want_inner, const char *who)
 {
     sphb200_ctx *ctx = r->ctx;
@@ -852,10 +977,93 @@ static sphb200_status ckAcousticHalf(sphb200_relation *inner, sphb200_relation *
     b->acoustic_max_valid = false;
     return SPHB200_OK;
 }
+
+// kind 0: PressureForceFromFluid, 1: ViscousForceFromFluid
+template <int D, class R>
+static sphb200_status ckForceFromFluid(sphb200_relation *contact, int kind, int corrected)
+{
+    sphb200_ctx *ctx = contact->ctx;
+    sphb200_body *b = contact->body;
+    const char *who = kind ? "ck_viscous_force_from_fluid" : "ck_pressure_force_from_fluid";
+    const char *name = kind ? "ViscousForceFromFluid" : "PressureForceFromFluid";
+    const char *prev_name = kind ? "PreviousViscousForceFromFluid" : "PreviousPressureForceFromFluid";
+    SPHB_TRY(ckCheck(contact, false, who));
+    if (b->own_end <= b->own_begin)
+        return SPHB200_OK;
+    SPHB_TRY((ensurePacked<D, R>(b)));
+    R *force, *prev, *fprior, *vol, *vel_ave = nullptr, *acc_ave = nullptr, *nrm = nullptr;
+    SPHB_TRY(getVarPtr<R>(b, name, D, &force));
+    SPHB_TRY(getVarPtr<R>(b, prev_name, D, &prev, true));
+    SPHB_TRY(getVarPtr<R>(b, "ForcePrior", D, &fprior, true));
+    SPHB_TRY(getVarPtr<R>(b, "VolumetricMeasure", 1, &vol, true));
+    if (b->find("Velocity"))
+        SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel_ave));
+    if (b->find("Acceleration"))
+        SPHB_TRY(getVarPtr<R>(b, "Acceleration", D, &acc_ave));
+    if (kind == 0)
+    {
+        if (!b->find("NormalDirection"))
+            return ctx->fail(SPHB200_ERR_NOT_FOUND, std::string(who) + ": the structure has no NormalDirection");
+        SPHB_TRY(getVarPtr<R>(b, "NormalDirection", D, &nrm));
+    }
+    const R h = b->P<D, R>().h;
+    auto *xV = static_cast<const typename Real4<R>::type *>(b->xV.p);
+    if (contact->targets.empty())
+        SPHB_CUDA(ctx, cudaMemsetAsync(force + b->own_begin * D, 0, size_t(b->own_end - b->own_begin) * D * sizeof(R), ctx->stream));
+    for (size_t t = 0; t < contact->targets.size(); ++t)
+    {
+        sphb200_body *f = contact->targets[t];
+        SPHB_TRY((ensurePacked<D, R>(f)));
+        SPHB_TRY(ensureList(contact, t));
+        R *t_vel, *B_t = nullptr;
+        SPHB_TRY(getVarPtr<R>(f, "Velocity", D, &t_vel, true));
+        if (corrected)
+        {
+            if (!f->find("LinearCorrectionMatrix"))
+                return ctx->fail(SPHB200_ERR_NOT_FOUND, std::string(who) + ": the fluid has no LinearCorrectionMatrix (ck_linear_correction_matrix)");
+            SPHB_TRY(getVarPtr<R>(f, "LinearCorrectionMatrix", D * D, &B_t));
+        }
+        auto *xVt = static_cast<const typename Real4<R>::type *>(f->xV.p);
+        const R hf = f->P<D, R>().h;
+        const TabKernelP<R> kc = makeTabKernel<D, R>(h, hf);
+        if (kind == 0)
+        {
+            R *t_rho, *t_mass, *t_p, *t_fp;
+            SPHB_TRY(getVarPtr<R>(f, "Density", 1, &t_rho, true));
+            SPHB_TRY(getVarPtr<R>(f, "Mass", 1, &t_mass, true));
+            SPHB_TRY(getVarPtr<R>(f, "Pressure", 1, &t_p, true));
+            SPHB_TRY(getVarPtr<R>(f, "ForcePrior", D, &t_fp, true));
+            const CkRiemann<D, R> rs = ckRiemannOf<D, R>(f);
+            k_ck_fsi_pressure<D, R><<<CK_GRID(b)>>>(b->own_begin, b->own_end, t == 0, xV, xVt, ckListOf(contact->lists[t]), kc, rs.rho0c0, rs.inv_c0,
+                                                    vel_ave, acc_ave, nrm, vol, t_vel, t_rho, t_mass, t_p, t_fp, B_t, force);
+        }
+        else
+            k_ck_fsi_viscous<D, R><<<CK_GRID(b)>>>(b->own_begin, b->own_end, t == 0, xV, xVt, ckListOf(contact->lists[t]), kc, R(f->mu), hf * hf, vel_ave,
+                                                   vol, t_vel, B_t, force);
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    k_ck_force_prior_update<R><<<gridFor((b->own_end - b->own_begin) * D, 256), 256, 0, ctx->stream>>>(b->own_begin * D, b->own_end * D, fprior, force, prev);
+    SPHB_LAUNCH_CHECK(ctx);
+    return SPHB200_OK;
+}
 } // namespace sphb
 
 extern "C"
 {
+sphb200_status sphb200_ck_pressure_force_from_fluid(sphb200_relation *contact, int corrected)
+{
+    if (!contact)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(contact->ctx->device);
+    return SPHB_DISPATCH(contact->ctx, ckForceFromFluid, contact, 0, corrected);
+}
+sphb200_status sphb200_ck_viscous_force_from_fluid(sphb200_relation *contact, int corrected)
+{
+    if (!contact)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(contact->ctx->device);
+    return SPHB_DISPATCH(contact->ctx, ckForceFromFluid, contact, 1, corrected);
+}
 sphb200_status sphb200_ck_advection_step_setup(sphb200_body *b)
 {
     if (!b)

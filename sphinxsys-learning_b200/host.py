@@ -239,6 +239,12 @@ class SPHSystem:
     def ck_free_surface_indication(self, inner, contact=None):
         self.check(self.lib.sphb200_ck_free_surface_indication(inner.h, contact.h if contact else None))
 
+    def ck_pressure_force_from_fluid(self, contact, corrected=True):
+        self.check(self.lib.sphb200_ck_pressure_force_from_fluid(contact.h, int(corrected)))
+
+    def ck_viscous_force_from_fluid(self, contact, corrected=True):
+        self.check(self.lib.sphb200_ck_viscous_force_from_fluid(contact.h, int(corrected)))
+
     def ck_advection_step_setup(self, body):
         self.check(self.lib.sphb200_ck_advection_step_setup(body.h))
 

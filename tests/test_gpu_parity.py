@@ -202,6 +202,49 @@ def test_ck_dambreak_2d_single_loop(pk, gpu, oracle, real_bytes):
     assert abs(g.mechanical_energy() - o.mechanical_energy()) < (1e-9 if real_bytes == 8 else 1e-4)
 
 
+@pytest.mark.parametrize("ndim,dp,real_bytes,corrected", [(3, 0.05, 8, True), (3, 0.05, 8, False), (2, 0.025, 8, True), (3, 0.05, 4, True)])
+def test_ck_force_of_the_fluid_on_the_structure(pk, gpu, oracle, ndim, dp, real_bytes, corrected):
+    """row f4: FSI::PressureForceOnStructure / ViscousForceOnStructure (force_on_structure.hpp:61-137) with their
+    ForcePriorCK update, on the contact relation wall -> water of the dam break with a seeded fluid state, a moving and
+    accelerating structure, with and without the fluid's linear correction matrix; two calls (the second after the
+    fluid state changed) so that the Previous-force bookkeeping of ForcePrior is exercised"""
+    g, o = both(pk, gpu, oracle, pk.cases.DamBreakCK, ndim=ndim, dp=dp, real_bytes=real_bytes, with_observer=False)
+    out = {}
+    for name, c in (("gpu", g), ("oracle", o)):
+        S, w, s = c.sys, c.water, c.wall
+        w.set_fluid(1.0, 20.0, 0.05)
+        jitter(w, 0.2)
+        st = seeded_state(c, seed=11)
+        set_field(w, "Velocity", st["Velocity"])
+        set_field(w, "Density", st["Density"])
+        set_field(w, "Pressure", (400.0 * (st["Density"] - 1.0)).astype(st["Density"].dtype))
+        rng = np.random.default_rng(5)
+        set_field(s, "Velocity", rng.normal(0.0, 0.2, size=(s.n, ndim)).astype(st["Velocity"].dtype))
+        set_field(s, "Acceleration", rng.normal(0.0, 0.5, size=(s.n, ndim)).astype(st["Velocity"].dtype))
+        w.update_cell_list()
+        s.update_cell_list()
+        c.update_configuration(observer=False)
+        rel = S.contact(s, [w])
+        rel.update()
+        S.ck_linear_correction_matrix(c.inner, c.wall_contact, 0.5)
+        S.ck_pressure_force_from_fluid(rel, corrected)
+        S.ck_viscous_force_from_fluid(rel, corrected)
+        first = {nm: field(s, nm) for nm in ("PressureForceFromFluid", "ViscousForceFromFluid", "ForcePrior")}
+        set_field(w, "Velocity", (-0.5 * st["Velocity"]).astype(st["Velocity"].dtype))
+        S.ck_pressure_force_from_fluid(rel, corrected)
+        S.ck_viscous_force_from_fluid(rel, corrected)
+        out[name] = (first, {nm: field(s, nm) for nm in ("PressureForceFromFluid", "ViscousForceFromFluid", "ForcePrior")})
+    tol = FP_TOL[real_bytes]
+    for k in (0, 1):
+        for nm in ("PressureForceFromFluid", "ViscousForceFromFluid", "ForcePrior"):
+            a, b = out["gpu"][k][nm], out["oracle"][k][nm]
+            assert np.abs(b).max() > 0 and rel_l2(a, b) < tol, (k, nm, rel_l2(a, b))
+    # ForcePrior carries exactly the current forces (it started at zero): the Previous-force update telescopes
+    second = out["gpu"][1]
+    assert rel_l2(second["ForcePrior"], second["PressureForceFromFluid"] + second["ViscousForceFromFluid"]) < 10 * tol
+    assert rel_l2(out["gpu"][0]["PressureForceFromFluid"], second["PressureForceFromFluid"]) > 1e-3   # the state did change
+
+
 @pytest.mark.parametrize("real_bytes", [8, 4])
 def test_solid_contact_neighbor_builders(pk, gpu, oracle, real_bytes):
     """row f4: NeighborBuilderSelfContact (neighborhood.cpp:123-142: r < rc and r0 > rc on InitialPosition, over a body
