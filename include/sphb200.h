@@ -61,6 +61,14 @@ sphb200_status sphb200_ctx_set_pair_kernel(sphb200_ctx *ctx, int mode);
  * sigma0 = lattice number density (adaptation.cpp:26-60). */
 sphb200_status sphb200_body_create(sphb200_ctx *ctx, const char *name, int64_t n, double dp, double h_ratio,
                                    sphb200_body **out);
+/* The spacing of the body's cell-linked-list mesh.  The reference builds every body's cell list with the body's OWN cut-off
+ * radius (meshes/cell_linked_list.cpp:84-101 through its adaptation) and lets a contact search from a body with a larger
+ * kernel walk a deeper block of cells (SearchDepthContact, body_relations/base_body_relation.cpp:10-16); the accepted
+ * neighbour set does not depend on the target's cell size.  A contact relation whose targets have cells at least as large
+ * as the SOURCE's cut-off takes the single-pass masked search here, so a caller may widen a target's cells (a SolidBody
+ * wall with h = 1.15 dp searched by a fluid with h = 1.3 dp: spacing = 2.6 dp).  Invalidates the cell list and every
+ * relation of the body: call cell_list_update / relation_update afterwards. */
+sphb200_status sphb200_body_set_cell_spacing(sphb200_body *b, double spacing);
 /* WeaklyCompressibleFluid(rho0,c0) + Viscosity(mu) (materials/weakly_compressible_fluid.cpp:8-30) */
 sphb200_status sphb200_body_set_fluid(sphb200_body *b, double rho0, double c0, double mu);
 /* NeoHookeanSolid(rho0,E,nu) (materials/elastic_solid.cpp:54-80) */

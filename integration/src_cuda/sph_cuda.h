@@ -207,8 +207,24 @@ inline sphb200_relation *relationHandle(BaseContactRelation &r)
     if (!r.device_relation_)
     {
         std::vector<sphb200_body *> t;
+        sphb200_ctx *ctx = context(r.getSPHBody().getSPHSystem());
+        double src[12];
+        check(sphb200_body_info(bodyHandle(r.getSPHBody()), src), ctx, "ContactRelation");
         for (RealBody *b : r.getContactBodies())
-            t.push_back(bodyHandle(*b));
+        {
+            sphb200_body *tb = bodyHandle(*b);
+            // a target with a smaller kernel than the source (SolidBody wall, h = 1.15 dp, under a fluid with 1.3 dp): the
+            // reference searches a deeper block of its small cells (SearchDepthContact); the library widens the cells
+            // instead - same neighbour set, single-pass masked search.  One re-binning of the target, once.
+            double tar[12];
+            check(sphb200_body_info(tb, tar), ctx, "ContactRelation");
+            if (tar[7] < src[1] && dynamic_cast<RealBody *>(&r.getSPHBody()))
+            {
+                check(sphb200_body_set_cell_spacing(tb, src[1]), ctx, "ContactRelation: cell spacing of the target");
+                check(sphb200_cell_list_update(tb), ctx, "ContactRelation: re-binning the target");
+            }
+            t.push_back(tb);
+        }
         sphb200_relation *h = nullptr;
         check(sphb200_relation_contact_create(bodyHandle(r.getSPHBody()), t.data(), int(t.size()), &h), context(r.getSPHBody().getSPHSystem()),
               "ContactRelation");

@@ -35,6 +35,7 @@ SIGNATURES = {
     "sphb200_ctx_launch_count": (_i64, [_vp]),
     "sphb200_ctx_set_pair_kernel": (_i, [_vp, _i]),
     "sphb200_body_create": (_i, [_vp, _cp, _i64, _d, _d, _vpp]),
+    "sphb200_body_set_cell_spacing": (_i, [_vp, _d]),
     "sphb200_body_set_fluid": (_i, [_vp, _d, _d, _d]),
     "sphb200_body_set_elastic": (_i, [_vp, _d, _d, _d]),
     "sphb200_body_set_periodic": (_i, [_vp, _i, _d, _d]),

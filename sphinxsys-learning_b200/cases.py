@@ -86,7 +86,7 @@ def shell_normals(p, center, half_outer, half_inner):
 # ------------------------------------------------------------------------------------------------
 class DamBreak:
     def __init__(self, backend, ndim=3, dp=0.05, real_bytes=8, with_observer=True, fluid_box=None, tank=None, x_range=None,
-                 defer_configuration=False, fused_loop=True, wall_h_ratio=1.3, **sys_kw):
+                 defer_configuration=False, fused_loop=True, wall_h_ratio=1.15, widen_wall_cells=True, **sys_kw):
         """x_range: keep only the lattice planes with x in [x_lo, x_hi) (one slab of a decomposed run);
         defer_configuration: stop before the first cell list / configuration (the slab driver finishes)"""
         dtype = np.float64 if real_bytes == 8 else np.float32
@@ -129,9 +129,12 @@ class DamBreak:
         # ---- wall body (Solid: rho0 = 1, static)
         # The reference's wall is a SolidBody, smoothing length 1.15 dp (predefined_bodies.h:44-54).  The fluid-wall contact
         # uses the LARGER of the two kernels (neighborhood.cpp:75-80), i.e. the fluid's, so the wall's own h only sets the
-        # cell size of the wall's cell list: neighbour sets and sums are the same either way.  The default 1.3 keeps the
-        # wall's cells as large as the fluid's cut-off (single-pass masked search); wall_h_ratio=1.15 is the reference's.
+        # cell size of the wall's cell list, which neighbour sets do not depend on.  On the CUDA library the wall's cells
+        # are widened to the fluid's cut-off (sphb200_body_set_cell_spacing): the contact search then takes the
+        # single-pass masked path instead of the two-pass generic one.  The oracle keeps the reference's cells.
         self.wall = s = self.sys.add_body("WallBoundary", len(shell), dp, h_ratio=wall_h_ratio)
+        if widen_wall_cells and hasattr(s, "set_cell_spacing") and wall_h_ratio < w.h_ratio:
+            s.set_cell_spacing(w.info()["rc"])
         s.set_fluid(1.0, 1.0, 0.0)
         s.set("Position", shell)
         s.set("VolumetricMeasure", np.full(len(shell), vol, dtype))

@@ -120,16 +120,31 @@ static R latticeSigma0(const KernelP<R> &k, R dp)
 }
 
 template <int D, class R>
+static sphb200_status setMeshSpacing(sphb200_body *b, double spacing);
+
+template <int D, class R>
 static sphb200_status initBodyParams(sphb200_body *b)
 {
-    sphb200_ctx *ctx = b->ctx;
     BodyP<D, R> &P = b->P<D, R>();
     P.dp = R(b->dp);
     P.h = R(b->h_ratio) * R(b->dp);
     P.kern = makeKernel<D, R>(P.h);
     P.sigma0 = latticeSigma0<D, R>(P.kern, P.dp);
-    // Mesh ctor, base_mesh.cpp:6-16 with buffer_width = 2 and spacing = cut-off radius
-    P.mesh.spacing = P.kern.rc;
+    SPHB_TRY((setMeshSpacing<D, R>(b, double(P.kern.rc))));
+    P.per.mask = 0;
+    for (int d = 0; d < D; ++d)
+        P.per.lo[d] = P.per.hi[d] = P.per.L[d] = P.per.half_L[d] = R(0);
+    return SPHB200_OK;
+}
+
+// Mesh ctor, base_mesh.cpp:6-16 with buffer_width = 2; the reference's spacing is the body's own cut-off radius
+// (cell_linked_list.cpp:84-101 via the adaptation), sphb200_body_set_cell_spacing may choose a larger one
+template <int D, class R>
+static sphb200_status setMeshSpacing(sphb200_body *b, double spacing)
+{
+    sphb200_ctx *ctx = b->ctx;
+    BodyP<D, R> &P = b->P<D, R>();
+    P.mesh.spacing = R(spacing);
     u64 total = 1;
     for (int d = 0; d < D; ++d)
     {
@@ -144,9 +159,6 @@ static sphb200_status initBodyParams(sphb200_body *b)
     if (total >= (u64(1) << 31))
         return ctx->fail(SPHB200_ERR_INVALID, "cell-linked-list mesh has more than 2^31 cells");
     b->n_cells = int64_t(total);
-    P.per.mask = 0;
-    for (int d = 0; d < D; ++d)
-        P.per.lo[d] = P.per.hi[d] = P.per.L[d] = P.per.half_L[d] = R(0);
     return SPHB200_OK;
 }
 
@@ -339,6 +351,20 @@ sphb200_status sphb200_body_create(sphb200_ctx *ctx, const char *name, int64_t n
     sphb200_var_register(b, "Position", ctx->ndim, 1, nullptr);
     sphb200_var_register(b, "VolumetricMeasure", 1, 1, nullptr);
     *out = b;
+    return SPHB200_OK;
+}
+
+sphb200_status sphb200_body_set_cell_spacing(sphb200_body *b, double spacing)
+{
+    if (!b)
+        return SPHB200_ERR_INVALID;
+    sphb200_ctx *ctx = b->ctx;
+    if (!(spacing > 0))
+        return ctx->fail(SPHB200_ERR_INVALID, "body_set_cell_spacing: spacing must be positive");
+    cudaSetDevice(ctx->device);
+    SPHB_TRY(SPHB_DISPATCH(ctx, setMeshSpacing, b, spacing));
+    b->cell_list_valid = false; // the next cell_list_update bins on the new mesh; relations on the old one are stale
+    b->config_stamp++;
     return SPHB200_OK;
 }
 

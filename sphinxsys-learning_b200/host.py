@@ -321,6 +321,10 @@ class Body:
         self.h = h
         self.widths = {"Position": system.ndim, "VolumetricMeasure": 1}
 
+    def set_cell_spacing(self, spacing):
+        """widen the cells of this body's cell list (sphb200_body_set_cell_spacing); neighbour sets do not depend on it"""
+        self.sys.check(self.lib.sphb200_body_set_cell_spacing(self.h, float(spacing)))
+
     def set_fluid(self, rho0, c0, mu=0.0):
         self.sys.check(self.lib.sphb200_body_set_fluid(self.h, rho0, c0, mu))
 

@@ -245,6 +245,31 @@ def test_ck_force_of_the_fluid_on_the_structure(pk, gpu, oracle, ndim, dp, real_
     assert rel_l2(out["gpu"][0]["PressureForceFromFluid"], second["PressureForceFromFluid"]) > 1e-3   # the state did change
 
 
+@pytest.mark.parametrize("ndim,dp", [(3, 0.05), (2, 0.025)])
+def test_widened_target_cells_give_the_same_contact_neighbours(pk, gpu, oracle, ndim, dp):
+    """sphb200_body_set_cell_spacing: the wall (SolidBody, h = 1.15 dp as in the reference) binned on cells of the fluid's
+    cut-off takes the single-pass masked contact search; on its own cells (the reference's arrangement, search depth 2)
+    the generic two-pass search.  Same neighbour set as the oracle's either way, same fields after whole steps."""
+    wide = pk.cases.DamBreak(gpu, ndim=ndim, dp=dp, real_bytes=8, with_observer=False)
+    own = pk.cases.DamBreak(gpu, ndim=ndim, dp=dp, real_bytes=8, with_observer=False, widen_wall_cells=False)
+    ref = pk.cases.DamBreak(oracle, ndim=ndim, dp=dp, real_bytes=8, with_observer=False)
+    assert wide.wall.info()["spacing"] == wide.water.info()["rc"] and own.wall.info()["spacing"] < own.water.info()["rc"]
+    assert wide.wall.h_ratio == own.wall.h_ratio == 1.15
+    for c in (wide, own, ref):
+        jitter(c.water, 0.25)
+        c.water.update_cell_list()
+        c.update_configuration(observer=False)
+    assert wide.wall_contact.stats()["masked_search"] and not own.wall_contact.stats()["masked_search"]
+    sets = [pair_set(c.wall_contact, target=c.wall) for c in (wide, own, ref)]
+    assert len(sets[2]) > 1000 and np.array_equal(sets[0], sets[2]) and np.array_equal(sets[1], sets[2])
+    for _ in range(2):
+        rw, ro, rr = wide.advection_step(observer=False), own.advection_step(observer=False), ref.advection_step(observer=False)
+        assert rw[1] == ro[1] == rr[1] and abs(rw[0] - ro[0]) <= 1e-12 * ro[0]   # other summation order in the wall sums
+    for nm in ("Position", "Velocity", "Density", "Pressure", "Force"):
+        assert rel_l2(field(wide.water, nm), field(own.water, nm)) < 1e-12, nm
+        assert rel_l2(field(wide.water, nm), field(ref.water, nm)) < FP_TOL[8], nm
+
+
 @pytest.mark.parametrize("real_bytes", [8, 4])
 def test_solid_contact_neighbor_builders(pk, gpu, oracle, real_bytes):
     """row f4: NeighborBuilderSelfContact (neighborhood.cpp:123-142: r < rc and r0 > rc on InitialPosition, over a body
