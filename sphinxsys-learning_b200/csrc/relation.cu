@@ -586,11 +586,13 @@ static sphb200_status expandList(sphb200_relation *r, size_t k)
     SPHB_TRY(reserveList(ctx, L));
     if (n > 0)
     {
-        static bool attr_set = false; // per (D, R) instantiation
-        if (!attr_set)
+        // the opt-in is a per-device attribute of the function: remember it per (D, R) instantiation AND device
+        static bool attr_set[64] = {};
+        if (ctx->device < 0 || ctx->device >= 64 || !attr_set[ctx->device])
         {
             SPHB_CUDA(ctx, cudaFuncSetAttribute(k_expand_mask<D, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kExpandSmem)));
-            attr_set = true;
+            if (ctx->device >= 0 && ctx->device < 64)
+                attr_set[ctx->device] = true;
         }
         sphb200_body *tgt = r->targets[k];
         k_expand_mask<D, R><<<gridFor(n, kExpandBlock), kExpandBlock, kExpandSmem, ctx->stream>>>(
