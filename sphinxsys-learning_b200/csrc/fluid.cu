@@ -56,6 +56,8 @@ struct FluidP
     const StepCtl *ctl; // device-resident dt / exit flag of the sub-step loop, or null: dt is the kernel argument
 };
 
+template <class R>
+static int quadLanesK2();
 static sphb200_status ensureStepCtl(sphb200_ctx *ctx);
 
 // dt of this launch: the kernel argument, or the device-resident one; false: the loop has ended, return at once
@@ -1136,6 +1138,16 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
                 k_first_half_wall<D, R, G><<<148 * 4, 128, 0, ctx->stream>>>(UW.base, b->own_begin, b->own_end, UW.queue, rec_a, uw.t[0],
                                                                            makeTileKernelP<R>(kern_w), rho, mass, fprior, ws, fl.ctl);
                 SPHB_LAUNCH_CHECK(ctx);
+                const int quad = quadLanesK2<R>();
+                if (quad == 2)
+                    k_first_half_quad<D, R, G, 2><<<gridFor(U.n_groups * 2, 128), 128, 0, ctx->stream>>>(
+                        U.base, b->own_begin, b->own_end, U.n_groups, rec_a, rec_b, ulistOf(U), uw.t[0].u.count, makeTileKernelP<R>(P.kern), fl, dt,
+                        rho, mass, fprior, force, drho, vel, slot, vmm, ws);
+                else if (quad == 4)
+                    k_first_half_quad<D, R, G, 4><<<gridFor(U.n_groups * 4, 128), 128, 0, ctx->stream>>>(
+                        U.base, b->own_begin, b->own_end, U.n_groups, rec_a, rec_b, ulistOf(U), uw.t[0].u.count, makeTileKernelP<R>(P.kern), fl, dt,
+                        rho, mass, fprior, force, drho, vel, slot, vmm, ws);
+                else
                 k_first_half_tile<D, R, G, true><<<gridFor(U.n_groups, 128), 128, 0, ctx->stream>>>(
                     U.base, b->own_begin, b->own_end, U.n_groups, rec_a, rec_b, ulistOf(U), uw, makeTileKernelP<R>(P.kern),
                     makeTileKernelP<R>(kern_w), fl, dt, rho, mass, fprior, force, drho, vel, slot, vmm, ws);
@@ -1165,6 +1177,19 @@ static sphb200_status firstHalf(sphb200_relation *inner, sphb200_relation *wall,
 // lanes per union group in the 2nd-half kernel: 0 = one thread per group (k_second_half_tile), 2 / 4 = k_second_half_quad
 // Measured at 20.1 M particles (B200, ms per launch): fp64 tile 8.61, 2 lanes 7.99, 4 lanes 8.36; fp32 tile 3.80, 2 lanes 4.63,
 // 4 lanes 4.54 (fp32 is issue-bound: the duplicated member state and the shuffles cost more than the merged sectors give).
+#ifndef SPHB_QUAD_K2_DEFAULT_F64
+#define SPHB_QUAD_K2_DEFAULT_F64 0
+#endif
+// the same for the 1st-half kernel (needs the wall pre-pass when there is a wall): env SPHB200_QUAD_K2 = 0 | 2 | 4
+template <class R>
+static int quadLanesK2()
+{
+    const char *e = getenv("SPHB200_QUAD_K2");
+    if (!e || !*e)
+        return sizeof(R) == 8 ? SPHB_QUAD_K2_DEFAULT_F64 : 0;
+    const int v = atoi(e);
+    return (v == 2 || v == 4) ? v : 0;
+}
 template <class R>
 static int quadLanes()
 {

@@ -844,6 +844,43 @@ def test_lanes_per_group_variants_of_the_second_half_agree(pk, gpu, oracle, ndim
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("ndim,dp,real_bytes,amp", [(3, 0.05, 8, 0.0), (3, 0.05, 8, 0.3), (3, 0.05, 4, 0.3), (2, 0.025, 8, 0.3)])
+def test_lanes_per_group_variants_of_the_first_half_agree(pk, gpu, oracle, ndim, dp, real_bytes, amp):
+    """k_first_half_quad (env SPHB200_QUAD_K2 = 2 | 4) against k_first_half_tile (0): same pairs, another summation
+    order - equal to rounding, each within the field tolerance of the oracle; uniform and non-uniform Vol"""
+    import os
+    out = {}
+    for flag in ("0", "2", "4", "oracle"):
+        os.environ["SPHB200_QUAD_K2"] = flag if flag != "oracle" else "0"
+        try:
+            c = pk.cases.DamBreak(oracle if flag == "oracle" else gpu, ndim=ndim, dp=dp, real_bytes=real_bytes)
+            if amp:
+                jitter(c.water, amp)
+                for nm, v in seeded_state(c).items():
+                    set_field(c.water, nm, v)
+                c.water.update_cell_list()
+                c.update_configuration()
+            c.sys.integration_1st_half(c.inner, c.wall_contact, True, 1e-4)
+            a = {nm: field(c.water, nm) for nm in ("Velocity", "Pressure", "DensityChangeRate", "Force")}
+            dt_a = c.sys.acoustic_dt(c.water)
+            # non-uniform Vol: the kernel then needs Vol_j from the record
+            vol = field(c.water, "VolumetricMeasure")
+            set_field(c.water, "VolumetricMeasure", (vol * (1.0 + 0.05 * np.sin(np.arange(len(vol))))).astype(vol.dtype))
+            c.sys.integration_1st_half(c.inner, c.wall_contact, True, 1e-4)
+            b = {nm: field(c.water, nm) for nm in ("Velocity", "Pressure", "DensityChangeRate", "Force")}
+            out[flag] = (a, b, dt_a)
+        finally:
+            os.environ.pop("SPHB200_QUAD_K2", None)
+    tight = 1e-12 if real_bytes == 8 else 2e-5
+    for flag in ("2", "4"):
+        assert abs(out[flag][2] - out["0"][2]) <= tight * out["0"][2]           # the fused max(c0 + |v|) reduction
+        for k in (0, 1):
+            for nm in out["0"][k]:
+                assert rel_l2(out[flag][k][nm], out["0"][k][nm]) < tight, (flag, k, nm)
+                assert rel_l2(out[flag][k][nm], out["oracle"][k][nm]) < FP_TOL[real_bytes], (flag, k, nm)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("ndim,dp,real_bytes", [(3, 0.05, 8), (2, 0.025, 8), (3, 0.05, 4)])
 def test_viscous_force_with_wall(pk, gpu, oracle, ndim, dp, real_bytes):
     """row a14: ViscousForceWithWall = ViscousForce<Inner<>> + ViscousForce<Contact<Wall>> (viscous_dynamics.hpp:35-53,92-115)
