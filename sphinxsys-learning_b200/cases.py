@@ -86,7 +86,7 @@ def shell_normals(p, center, half_outer, half_inner):
 # ------------------------------------------------------------------------------------------------
 class DamBreak:
     def __init__(self, backend, ndim=3, dp=0.05, real_bytes=8, with_observer=True, fluid_box=None, tank=None, x_range=None,
-                 defer_configuration=False, fused_loop=True, wall_h_ratio=1.15, widen_wall_cells=True, **sys_kw):
+                 defer_configuration=False, fused_loop=True, wall_h_ratio=1.15, widen_wall_cells=True, probes=None, **sys_kw):
         """x_range: keep only the lattice planes with x in [x_lo, x_hi) (one slab of a decomposed run);
         defer_configuration: stop before the first cell list / configuration (the slab driver finishes)"""
         dtype = np.float64 if real_bytes == 8 else np.float32
@@ -96,12 +96,15 @@ class DamBreak:
             DL, DH, DW = tank or (5.366, 2.0, 0.5)
             LL, LH, LW = fluid_box or (2.0, 1.0, 0.5)
             tank_sz, water_sz = [DL, DH, DW], [LL, LH, LW]
-            probes = [[DL, y, 0.5 * DW] for y in (0.01, 0.1, 0.2, 0.24, 0.252, 0.266)]
+            probes = probes or [[DL, y, 0.5 * DW] for y in (0.01, 0.1, 0.2, 0.24, 0.252, 0.266)]
         else:
             DL, DH = tank or (5.366, 5.366)
             LL, LH = fluid_box or (2.0, 1.0)
             tank_sz, water_sz = [DL, DH], [LL, LH]
-            probes = [[DL, 0.2]]
+            probes = probes or [[DL, 0.2]]
+        if probes is not None:   # other observation points than the reference main's (tests)
+            probes = [list(p) for p in probes]
+        self.probes = probes
         self.rho0, self.g = 1.0, 1.0
         self.U_ref = 2.0 * math.sqrt(self.g * water_sz[1])
         self.c0 = 10.0 * self.U_ref

@@ -201,7 +201,8 @@ class DistComm:
         return float(t.item())
 
     def allreduce_sum_array(self, arrays):
-        t = torch.as_tensor(np.asarray(arrays[0], dtype=np.int64), device=self.device)
+        a = np.asarray(arrays[0])
+        t = torch.as_tensor(a.astype(np.float64 if a.dtype.kind == "f" else np.int64), device=self.device)
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return t.cpu().numpy()
 
@@ -245,9 +246,12 @@ class SlabDamBreak:
     """tests/3d_examples/test_3d_dambreak/dambreak.cpp:159-195 over n_slabs slabs; same loop as cases.DamBreak"""
 
     def __init__(self, backend, comm, dp=0.05, real_bytes=8, device=0, stream=None, ndim=3, device_loop=True, fast_reconfigure=True,
-                 recut_interval=20, recut_threshold=0.05, peer_halo=None):
+                 recut_interval=20, recut_threshold=0.05, peer_halo=None, probes=None):
         """recut_interval / recut_threshold: every recut_interval advection steps the owned fluid per page is summed over
         the slabs and, when the fullest slab holds more than (1 + threshold) x the mean, the cuts move (SURVEY 8e; 0 = never);
+        probes: observation points (True: the reference main's six pressure probes).  Every slab carries the observer
+        body; a probe is evaluated by the slab that owns the page of its position (its neighbourhood lies in that slab's
+        owned + halo particles) and the values are summed over the slabs (SURVEY 8e: owner-rank evaluation);
         peer_halo: the per-sub-step halo records are pushed straight into the neighbour GPU's memory by the pack kernel
         (csrc/peer.cu; False: pack -> torch.distributed send/recv -> unpack; None: on unless env SPHB200_PEER_HALO=0);
         device_loop: dt / relaxation time / exit test of the sub-step loop on the device (False: one host round trip
@@ -286,7 +290,8 @@ class SlabDamBreak:
             P.has_left, P.has_right = r > 0, r + 1 < comm.n_slabs
             x_lo = self.mesh_lo[0] + (P.p_lo - 1) * self.spacing - dp
             x_hi = self.mesh_lo[0] + (P.p_hi + 1) * self.spacing + dp
-            P.case = c = cases.DamBreak(backend, ndim=ndim, dp=dp, real_bytes=real_bytes, with_observer=False,
+            P.case = c = cases.DamBreak(backend, ndim=ndim, dp=dp, real_bytes=real_bytes, with_observer=probes is not None,
+                                        probes=None if probes is True else probes,
                                         x_range=(x_lo, x_hi), defer_configuration=True, device=device, stream=stream)
             w, s = c.water, c.wall
             pos = w.get("Position").astype(np.float64) if w.n else np.zeros((0, ndim))
@@ -306,7 +311,9 @@ class SlabDamBreak:
             s.set_owned_pages(P.p_lo, P.p_hi)   # the wall is only ever a target; its owned pages serve the re-cut
             w.update_cell_list()
             s.update_cell_list()
-            c.update_configuration(observer=False)
+            if c.observer is not None:
+                c.observer.update_cell_list()
+            c.update_configuration(observer=c.observer is not None)
             c.sys.gravity_force(w, c.gravity)
             self.parts.append(P)
         if peer_halo is None:
@@ -539,7 +546,7 @@ class SlabDamBreak:
         self._move(lambda P: P.case.water, MIGRATE_VARS, t_real)
         for P in self.parts:
             P.case.water.update_cell_list()
-            P.case.update_configuration(observer=False)
+            P.case.update_configuration(observer=P.case.observer is not None)
         self._halo_maps()
         if self.recut_interval and self.n_advection % self.recut_interval == 0:
             self._pending_cuts = self.plan_recut()
@@ -571,7 +578,7 @@ class SlabDamBreak:
                     v[n_old:n_new] = block[:, col:col + v.shape[1]]
                     col += v.shape[1]
             w.update_cell_list()
-            P.case.update_configuration(observer=False)
+            P.case.update_configuration(observer=P.case.observer is not None)
         self._halo_maps()
 
     # ---- observables / inspection -------------------------------------------------------------------
@@ -581,6 +588,19 @@ class SlabDamBreak:
     def mechanical_energy(self):
         vals = [P.case.sys.total_mechanical_energy(P.case.water, self.gravity) if P.oe > P.ob else 0.0 for P in self.parts]
         return self.comm.allreduce([sum(vals)], "sum")
+
+    def probe_pressure(self):
+        """ObservedQuantityRecording<Real>("Pressure") of the observation points (general_interpolation.h:63-83): each probe
+        from the slab that owns the page of its position, summed over the slabs"""
+        vals = []
+        for P in self.parts:
+            c = P.case
+            pos = np.asarray(c.probes, dtype=np.float64)
+            page = np.clip(np.floor((pos[:, 0] - self.mesh_lo[0]) / self.spacing).astype(np.int64), 0, self.cells[0] - 1)
+            mine = (page >= P.p_lo) & (page < P.p_hi)
+            v = np.asarray(c.probe_pressure(), dtype=np.float64)
+            vals.append(np.where(mine, v, 0.0))
+        return self.comm.allreduce_sum_array(vals)
 
     def owned(self, name):
         """(global ids, values) of the locally owned particles, on the host"""

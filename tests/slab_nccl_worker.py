@@ -22,8 +22,9 @@ lr = int(os.environ.get("LOCAL_RANK", "0"))
 torch.cuda.set_device(lr)
 dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
 comm = slab.DistComm(torch.device("cuda", lr))
-many = slab.SlabDamBreak(pk.host, comm, dp=dp, real_bytes=8, device=lr)
-one = pk.cases.DamBreak(pk.host, ndim=3, dp=dp, real_bytes=8, with_observer=False, device=lr) if comm.rank == 0 else None
+PROBES = [[x, y, 0.25] for x in (0.31, 0.93, 1.02, 1.49, 1.97) for y in (0.12, 0.55)]
+many = slab.SlabDamBreak(pk.host, comm, dp=dp, real_bytes=8, device=lr, probes=PROBES)
+one = pk.cases.DamBreak(pk.host, ndim=3, dp=dp, real_bytes=8, with_observer=True, probes=PROBES, device=lr) if comm.rank == 0 else None
 if one is not None:
     pos0 = one.water.get("Position").astype(np.float64)
     oid0, _ = one.water.ids()
@@ -33,9 +34,11 @@ if one is not None:
     gid_by_oid[oid0] = gid_sorted
 for s in range(steps):
     rn = many.advection_step()
+    pn = many.probe_pressure()                       # owner-rank evaluation + all-reduce(sum): every rank takes part
     if one is not None:
         r1 = one.advection_step()
         assert r1 == rn, ("(Dt, sub-steps) differ at advection step", s, r1, rn)
+        assert np.allclose(np.asarray(one.probe_pressure()), pn, rtol=1e-9, atol=1e-12), ("probe pressures differ at step", s)
 en = many.mechanical_energy()
 nf = many.n_fluid()
 worst = {}

@@ -209,3 +209,22 @@ def test_migration_and_recut_over_a_collapsing_column(pk, gpu, slab, monkeypatch
     worst = _compare_owned_with_single(one, many, dp, 1e-7)
     e1, en = one.mechanical_energy(), many.mechanical_energy()
     assert abs(e1 - en) <= 1e-9 * abs(e1), (e1, en, worst)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_slabs", [2, 4])
+def test_probes_are_evaluated_by_the_owning_slab(pk, gpu, slab, n_slabs):
+    """observables of a decomposed run - the pressure probes (ObservingAQuantity) come from the slab that owns
+    the probe's page, summed over the slabs; equal to the undecomposed run's, also for probes next to a cut"""
+    dp = 0.05
+    probes = [[x, y, 0.25] for x in (0.31, 0.93, 1.02, 1.49, 1.97) for y in (0.12, 0.55)]
+    one = pk.cases.DamBreak(gpu, ndim=3, dp=dp, real_bytes=8, with_observer=True, probes=probes)
+    many = slab.SlabDamBreak(gpu, slab.LocalComm(n_slabs), dp=dp, real_bytes=8, probes=probes)
+    cut_x = [many.mesh_lo[0] + c * many.spacing for c in many.cuts[1:-1]]
+    assert any(min(abs(p[0] - cx) for cx in cut_x) < 2 * many.spacing for p in probes)     # some probes sit near a cut
+    for s in range(6):
+        r1, rn = one.advection_step(), many.advection_step()
+        assert r1 == rn
+        a, b = np.asarray(one.probe_pressure()), np.asarray(many.probe_pressure())
+        assert np.allclose(a, b, rtol=1e-9, atol=1e-12), (s, a, b)
+    assert np.abs(a).min() > 1e-4 and np.abs(a).max() > 0.02          # pressure has built up at every probe
