@@ -20,6 +20,7 @@ slab per process.
 """
 import math
 import os
+import sys
 
 import numpy as np
 
@@ -320,7 +321,17 @@ class SlabDamBreak:
             peer_halo = os.environ.get("SPHB200_PEER_HALO", "1") != "0"
         self.peer_halo, self._epoch = bool(peer_halo), [0, 0]
         if self.peer_halo:
-            self._peer_setup()
+            # the mapping of a neighbour's memory can be refused (no peer access between two GPUs, IPC disabled in a
+            # container): every rank must then take the send/recv transport - agree on it before the first exchange
+            ok, why = 1.0, ""
+            try:
+                self._peer_setup()
+            except Exception as e:  # noqa: BLE001 - any failure of the set-up means "no peer path here"
+                ok, why = 0.0, repr(e)
+            if comm.allreduce([ok], "min") < 1.0:
+                if why:
+                    print(f"[sphb200 slab] halo push into peer memory unavailable ({why}); using send/recv", file=sys.stderr, flush=True)
+                self.peer_halo = False
         self._halo_maps()
         self.time, self.dt, self.n_advection, self.n_acoustic = 0.0, 0.0, 0, 0
 

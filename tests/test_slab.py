@@ -228,3 +228,18 @@ def test_probes_are_evaluated_by_the_owning_slab(pk, gpu, slab, n_slabs):
         a, b = np.asarray(one.probe_pressure()), np.asarray(many.probe_pressure())
         assert np.allclose(a, b, rtol=1e-9, atol=1e-12), (s, a, b)
     assert np.abs(a).min() > 1e-4 and np.abs(a).max() > 0.02          # pressure has built up at every probe
+
+
+@pytest.mark.gpu
+def test_refused_peer_mapping_falls_back_to_send_recv(pk, gpu, slab, monkeypatch, capsys):
+    """a box that refuses the mapping of a neighbour's memory: all slabs agree on the send/recv transport (another
+    transport for the same records, not another compute path) and the run is unchanged"""
+    def refuse(self):
+        raise RuntimeError("peer access denied (test)")
+    monkeypatch.setattr(slab.SlabDamBreak, "_peer_setup", refuse)
+    one = pk.cases.DamBreak(gpu, ndim=3, dp=0.05, real_bytes=8, with_observer=False)
+    many = slab.SlabDamBreak(gpu, slab.LocalComm(3), dp=0.05, real_bytes=8, peer_halo=True)
+    assert many.peer_halo is False and "unavailable" in capsys.readouterr().err
+    for _ in range(3):
+        assert one.advection_step() == many.advection_step()
+    assert abs(one.mechanical_energy() - many.mechanical_energy()) <= 1e-9 * abs(one.mechanical_energy())
