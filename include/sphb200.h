@@ -236,6 +236,11 @@ sphb200_status sphb200_observe(sphb200_relation *contact, const char *name, int 
  * (shared_ck/particle_dynamics/fluid_dynamics/density_regularization.hpp:42-111): CompressionSummation = W0 Vref_i + sum W_ij Vref_j,
  * Compression = max(sum, 1) | sum, Density = Compression * rho0; "VolumetricMeasureRef" is copied from VolumetricMeasure when first used */
 sphb200_status sphb200_ck_density_regularization(sphb200_relation *inner, sphb200_relation *contact_or_null, int free_surface);
+/* the same as its two reference objects: InteractionDynamicsCK<..., CompressionSummation<Inner<>, Contact<>>>::exec()
+ * (density_regularization.hpp:42-83: the sums into "CompressionSummation") and StateDynamics<..., DensityRegularization<...,
+ * FreeSurface | Internal>>::exec() (:103-111: Compression = max(sum, 1) | sum, Density = Compression rho0) */
+sphb200_status sphb200_ck_compression_summation(sphb200_relation *inner, sphb200_relation *contact_or_null);
+sphb200_status sphb200_ck_density_regularize(sphb200_body *body, int free_surface);
 /* LinearCorrectionMatrix<Inner<WithUpdate>>(alpha) + <Contact> (general_dynamics/kernel_correction_ck.hpp:36-96): B = -sum r_ij (nablaW_ij V_j)^T,
  * then B <- w B^-1(Tikhonov, 1e-8) + (1 - w) I with w = det / (det + max(alpha - det, 0)); variable "LinearCorrectionMatrix" (ndim x ndim) */
 sphb200_status sphb200_ck_linear_correction_matrix(sphb200_relation *inner, sphb200_relation *contact_or_null, double alpha);

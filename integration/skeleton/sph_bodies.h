@@ -51,6 +51,7 @@ class SingleVariable : public BaseVariable
     DataType *Data() { return &value_; }
     DataType getValue() const { return value_; }
     void setValue(const DataType &v) { value_ = v; }
+    void incrementValue(const DataType &v) { value_ += v; }
 
   private:
     DataType value_;
@@ -266,6 +267,8 @@ class SPHSystem
     size_t RestartStep() const { return restart_step_; }
     template <typename DataType>
     DataType *getSystemVariableDataByName(const std::string &) { return physical_time_.Data(); }
+    template <typename DataType>
+    SingleVariable<DataType> *getSystemVariableByName(const std::string &) { return &physical_time_; }
     void addRealBody(RealBody *b) { real_bodies_.push_back(b); }
     void addRelation(SPHRelation *r) { relations_.push_back(r); }
     inline void initializeSystemCellLinkedLists(); // sph_system.cpp:58-66

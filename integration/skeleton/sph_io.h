@@ -40,9 +40,23 @@ class BaseQuantityRecording
     std::string body_name_;
 };
 
-template <class LocalReduceMethodType, class ExecutionPolicy = SPHINXSYS_DEFAULT_POLICY>
-class ReducedQuantityRecording : public BaseQuantityRecording // io_observation.h:123-170
+// The reference declares the recorders as `template <typename...> class X;` with one specialisation for the classic
+// form X<Method> and one for the CK form X<ExecutionPolicy, Method> (io_observation.h, io_observation_ck.h)
+template <typename...>
+class ReducedQuantityRecording;
+template <typename...>
+class ObservedQuantityRecording;
+template <class>
+struct DefaultPolicyFor // keeps the policy a dependent type: the back end's specialisations are defined after this header
 {
+    using type = SPHINXSYS_DEFAULT_POLICY;
+};
+
+template <class LocalReduceMethodType>
+class ReducedQuantityRecording<LocalReduceMethodType> : public BaseQuantityRecording // io_observation.h:123-170
+{
+    using ExecutionPolicy = typename DefaultPolicyFor<LocalReduceMethodType>::type;
+
   public:
     template <class DynamicsIdentifier, typename... Args>
     ReducedQuantityRecording(DynamicsIdentifier &identifier, Args &&...args)
@@ -63,9 +77,11 @@ class ReducedQuantityRecording : public BaseQuantityRecording // io_observation.
     std::vector<std::vector<double>> rows_;
 };
 
-template <typename DataType, class ExecutionPolicy = SPHINXSYS_DEFAULT_POLICY>
-class ObservedQuantityRecording : public BaseQuantityRecording // io_observation.h:56-120
+template <typename DataType>
+class ObservedQuantityRecording<DataType> : public BaseQuantityRecording // io_observation.h:56-120
 {
+    using ExecutionPolicy = typename DefaultPolicyFor<DataType>::type;
+
   public:
     ObservedQuantityRecording(const std::string &quantity_name, BaseContactRelation &contact_relation)
         : BaseQuantityRecording(contact_relation.getSPHBody().getSPHSystem(), contact_relation.getSPHBody().getName()),

@@ -17,9 +17,11 @@ class ParallelCudaPolicy;
 #include "sph_bodies.h"
 #include "sph_dynamics.h"
 #include "sph_io.h"
+#include "sph_ck.h"
 #ifdef SPHINXSYS_USE_CUDA
 #include "sph_cuda.h"
 #include "sph_cuda_dynamics.h"
+#include "sph_cuda_ck.h"
 #else
 namespace SPH
 {

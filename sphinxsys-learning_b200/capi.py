@@ -100,6 +100,8 @@ SIGNATURES = {
     "sphb200_ck_density_regularization": (_i, [_vp, _vp, _i]),
     "sphb200_ck_linear_correction_matrix": (_i, [_vp, _vp, _d]),
     "sphb200_ck_free_surface_indication": (_i, [_vp, _vp]),
+    "sphb200_ck_compression_summation": (_i, [_vp, _vp]),
+    "sphb200_ck_density_regularize": (_i, [_vp, _i]),
     "sphb200_ck_pressure_force_from_fluid": (_i, [_vp, _i]),
     "sphb200_ck_viscous_force_from_fluid": (_i, [_vp, _i]),
     "sphb200_ck_advection_step_setup": (_i, [_vp]),

@@ -705,8 +705,9 @@ static sphb200_status volRef(sphb200_body *b, R **out)
 }
 #define CK_GRID(b) gridFor((b)->own_end - ((b)->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream
 
+// stage 1: CompressionSummation (inner + contact sums), 2: DensityRegularization (the update), 3: both
 template <int D, class R>
-static sphb200_status ckDensityRegularization(sphb200_relation *inner, sphb200_relation *contact, int free_surface)
+static sphb200_status ckDensityRegularization(sphb200_relation *inner, sphb200_relation *contact, int free_surface, int stage = 3)
 {
     sphb200_ctx *ctx = inner->ctx;
     sphb200_body *b = inner->body;
@@ -724,9 +725,12 @@ static sphb200_status ckDensityRegularization(sphb200_relation *inner, sphb200_r
     SPHB_TRY(ensureList(inner, 0));
     const R h = b->P<D, R>().h;
     auto *xV = static_cast<const typename Real4<R>::type *>(b->xV.p);
+    if (stage & 1)
+    {
     k_ck_compression<D, R><<<CK_GRID(b)>>>(b->own_begin, b->own_end, 1, xV, xV, ckListOf(inner->lists[0]), makeTabKernel<D, R>(h, h), vref, vref, csum);
     SPHB_LAUNCH_CHECK(ctx);
-    for (size_t t = 0; contact && t < contact->targets.size(); ++t)
+    }
+    for (size_t t = 0; (stage & 1) && contact && t < contact->targets.size(); ++t)
     {
         sphb200_body *tb = contact->targets[t];
         SPHB_TRY((ensurePacked<D, R>(tb)));
@@ -737,6 +741,27 @@ static sphb200_status ckDensityRegularization(sphb200_relation *inner, sphb200_r
                                                ckListOf(contact->lists[t]), makeTabKernel<D, R>(h, tb->P<D, R>().h), vref, tref, csum);
         SPHB_LAUNCH_CHECK(ctx);
     }
+    if (stage & 2)
+    {
+        k_ck_regularize<R><<<gridFor(b->own_end - b->own_begin, 256), 256, 0, ctx->stream>>>(b->own_begin, b->own_end, free_surface, R(b->rho0), csum, comp, rho);
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    b->rec_b_valid = false;
+    return SPHB200_OK;
+}
+
+template <int D, class R>
+static sphb200_status ckRegularizeOnly(sphb200_body *b, int free_surface)
+{
+    sphb200_ctx *ctx = b->ctx;
+    if (b->own_end <= b->own_begin)
+        return SPHB200_OK;
+    if (!b->find("CompressionSummation"))
+        return ctx->fail(SPHB200_ERR_NOT_FOUND, "ck_density_regularize: CompressionSummation has not been computed (ck_compression_summation)");
+    R *csum, *comp, *rho;
+    SPHB_TRY(getVarPtr<R>(b, "CompressionSummation", 1, &csum));
+    SPHB_TRY(getVarPtr<R>(b, "Compression", 1, &comp));
+    SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
     k_ck_regularize<R><<<gridFor(b->own_end - b->own_begin, 256), 256, 0, ctx->stream>>>(b->own_begin, b->own_end, free_surface, R(b->rho0), csum, comp, rho);
     SPHB_LAUNCH_CHECK(ctx);
     b->rec_b_valid = false;
@@ -1111,7 +1136,21 @@ sphb200_status sphb200_ck_density_regularization(sphb200_relation *inner, sphb20
     if (!inner || (contact && contact->ctx != inner->ctx))
         return SPHB200_ERR_INVALID;
     cudaSetDevice(inner->ctx->device);
-    return SPHB_DISPATCH(inner->ctx, ckDensityRegularization, inner, contact, free_surface);
+    return SPHB_DISPATCH(inner->ctx, ckDensityRegularization, inner, contact, free_surface, 3);
+}
+sphb200_status sphb200_ck_compression_summation(sphb200_relation *inner, sphb200_relation *contact)
+{
+    if (!inner || (contact && contact->ctx != inner->ctx))
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(inner->ctx->device);
+    return SPHB_DISPATCH(inner->ctx, ckDensityRegularization, inner, contact, 0, 1);
+}
+sphb200_status sphb200_ck_density_regularize(sphb200_body *b, int free_surface)
+{
+    if (!b)
+        return SPHB200_ERR_INVALID;
+    cudaSetDevice(b->ctx->device);
+    return SPHB_DISPATCH(b->ctx, ckRegularizeOnly, b, free_surface);
 }
 sphb200_status sphb200_ck_linear_correction_matrix(sphb200_relation *inner, sphb200_relation *contact, double alpha)
 {

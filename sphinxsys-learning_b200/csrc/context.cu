@@ -51,6 +51,9 @@ sphb200_status getVar(sphb200_body *b, const char *name, int width, bool evolvin
     if (v->width != width)
         return b->ctx->fail(SPHB200_ERR_INVALID, std::string("variable '") + name + "' registered with width " +
                                                      std::to_string(v->width) + ", requested " + std::to_string(width));
+    // a dynamics that needs the field to follow its particle through the cell-order sort gets that, whoever registered it
+    if (evolving && !v->evolving)
+        v->evolving = true;
     *out = v;
     return SPHB200_OK;
 }

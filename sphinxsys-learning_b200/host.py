@@ -239,6 +239,12 @@ class SPHSystem:
     def ck_free_surface_indication(self, inner, contact=None):
         self.check(self.lib.sphb200_ck_free_surface_indication(inner.h, contact.h if contact else None))
 
+    def ck_compression_summation(self, inner, contact=None):
+        self.check(self.lib.sphb200_ck_compression_summation(inner.h, contact.h if contact else None))
+
+    def ck_density_regularize(self, body, free_surface=True):
+        self.check(self.lib.sphb200_ck_density_regularize(body.h, int(free_surface)))
+
     def ck_pressure_force_from_fluid(self, contact, corrected=True):
         self.check(self.lib.sphb200_ck_pressure_force_from_fluid(contact.h, int(corrected)))
 

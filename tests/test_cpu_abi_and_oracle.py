@@ -45,22 +45,25 @@ def test_cpp_adapter_main_builds_and_fails_loudly_without_a_gpu(pk):
 
 
 def test_reference_main_compiles_unmodified_on_the_cuda_policy():
-    """integration/: the reference's tests/3d_examples/test_3d_dambreak/dambreak.cpp, read where it lies and not a byte
-    changed, compiles against the class skeleton + the CUDA execution policy (src_cuda) + libsphb200; without a GPU the
+    """integration/: the reference's tests/3d_examples/test_3d_dambreak/dambreak.cpp and the CK main
+    tests/tests_sycl/3d_examples/test_3d_dambreak_sycl/dambreak.cpp, read where they lie and not a byte changed, compile against the class skeleton + the CUDA execution policy (src_cuda) + libsphb200; without a GPU the
     binary fails loudly (the reference's convention: message + exit 1)"""
     import subprocess
     import torch
     subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "integration")])
-    exe = os.path.join(ROOT, "integration", "_build", "test_3d_dambreak_cuda")
-    if not os.path.exists("/root/reference") and not os.path.exists(exe):
-        pytest.skip("reference tree absent and no prebuilt binary")
-    assert os.path.exists(exe)
     mk = open(os.path.join(ROOT, "integration", "Makefile")).read()
-    assert "$(REF)/tests/3d_examples/test_3d_dambreak/dambreak.cpp" in mk  # compiled from the reference tree, not from a copy
-    if torch.cuda.is_available():
-        pytest.skip("a GPU is present: the run itself is covered by the gpu tests")
-    r = subprocess.run([exe, "--state_recording=0"], capture_output=True, text=True)
-    assert r.returncode == 1 and "no CUDA device" in r.stdout + r.stderr
+    # compiled from the reference tree, not from copies: the classic main and its CK twin of the SYCL test tree
+    assert "$(REF)/tests/3d_examples/test_3d_dambreak/dambreak.cpp" in mk
+    assert "$(REF)/tests/tests_sycl/3d_examples/test_3d_dambreak_sycl/dambreak.cpp" in mk
+    for name in ("test_3d_dambreak_cuda", "test_3d_dambreak_ck_cuda"):
+        exe = os.path.join(ROOT, "integration", "_build", name)
+        if not os.path.exists("/root/reference") and not os.path.exists(exe):
+            pytest.skip("reference tree absent and no prebuilt binary")
+        assert os.path.exists(exe), name
+        if torch.cuda.is_available():
+            continue  # a GPU is present: the run itself is covered by the gpu tests
+        r = subprocess.run([exe, "--state_recording=0"], capture_output=True, text=True)
+        assert r.returncode == 1 and "no CUDA device" in r.stdout + r.stderr, name
 
 
 def test_product_package_never_touches_the_oracle():

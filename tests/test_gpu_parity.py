@@ -768,6 +768,41 @@ def test_reference_main_on_the_cuda_policy_equals_the_python_harness(pk, gpu, tm
 
 
 @pytest.mark.gpu
+def test_reference_ck_main_on_the_cuda_policy_equals_the_python_harness(pk, gpu, tmp_path):
+    """row f3: the reference's unmodified CK dam-break main of the SYCL test tree (integration/_build/test_3d_dambreak_ck_cuda:
+    MainExecutionPolicy = the CUDA policy, every InteractionDynamicsCK / StateDynamics / ReduceDynamicsCK it constructs routed
+    to csrc/ck.cu) runs to t = 20 and records the same 21 energy samples and probe series as the Python harness
+    (cases.DamBreakCK) driving the same library"""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "integration", "_build", "test_3d_dambreak_ck_cuda")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-s", "-C", os.path.join(root, "integration")])
+    if not os.path.exists(exe):
+        pytest.skip("integration binary was not built (needs the reference tree at build time)")
+    r = subprocess.run([exe, "--state_recording=0"], capture_output=True, text=True, cwd=tmp_path, timeout=900)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+    energy = np.loadtxt(tmp_path / "output" / "WaterBody_TotalMechanicalEnergy.dat", skiprows=1)
+    probes = np.loadtxt(tmp_path / "output" / "FluidObserver_Pressure.dat", skiprows=1)
+    c = pk.cases.DamBreakCK(gpu, ndim=3, dp=0.05, real_bytes=8)
+    e, p, t = [c.mechanical_energy()], [c.probe_pressure().copy()], [0.0]
+    while c.time < 20.0:
+        integ = 0.0
+        while integ < 1.0:
+            t0 = c.time
+            c.advection_step()
+            integ += c.time - t0
+            p.append(c.probe_pressure().copy())
+        e.append(c.mechanical_energy())
+        t.append(c.time)
+    assert energy.shape == (len(e), 2) and probes.shape == (len(p), 7)
+    assert np.allclose(energy[:, 0], t, rtol=1e-12, atol=0) and np.allclose(energy[:, 1], e, rtol=1e-11, atol=0)
+    assert np.allclose(probes[:, 1:], np.asarray(p), rtol=1e-9, atol=1e-12)
+    assert abs(e[0] - 0.5) < 1e-12 and e[-1] < 0.25
+
+
+@pytest.mark.gpu
 def test_run_level_observables_against_the_reference_fixtures(pk, gpu):
     """the CUDA path against the FULL stored series of the reference's own regression fixtures (tests/golden),
     same assertions as the CPU oracle's pin (tests/test_cpu_abi_and_oracle.py):
