@@ -213,6 +213,16 @@ class Solid : public BaseMaterial
   public:
     explicit Solid(Real rho0 = Real(1)) : BaseMaterial(rho0) {}
 };
+class NeoHookeanSolid : public Solid // materials/elastic_solid.h:120-140 (constants only)
+{
+  public:
+    NeoHookeanSolid(Real rho0, Real youngs_modulus, Real poisson_ratio) : Solid(rho0), E_(youngs_modulus), nu_(poisson_ratio) {}
+    Real YoungsModulus() const { return E_; }
+    Real PoissonRatio() const { return nu_; }
+
+  private:
+    Real E_, nu_;
+};
 
 // adaptations/adaptation.h: spacing and smoothing-length ratio
 class SPHAdaptation
@@ -270,6 +280,7 @@ class SPHSystem
     template <typename DataType>
     SingleVariable<DataType> *getSystemVariableByName(const std::string &) { return &physical_time_; }
     void addRealBody(RealBody *b) { real_bodies_.push_back(b); }
+    const std::vector<RealBody *> &getRealBodies() const { return real_bodies_; }
     void addRelation(SPHRelation *r) { relations_.push_back(r); }
     inline void initializeSystemCellLinkedLists(); // sph_system.cpp:58-66
     inline void initializeSystemConfigurations();  // sph_system.cpp:68-77

@@ -18,10 +18,12 @@ class ParallelCudaPolicy;
 #include "sph_dynamics.h"
 #include "sph_io.h"
 #include "sph_ck.h"
+#include "sph_solid.h"
 #ifdef SPHINXSYS_USE_CUDA
 #include "sph_cuda.h"
 #include "sph_cuda_dynamics.h"
 #include "sph_cuda_ck.h"
+#include "sph_cuda_solid.h"
 #else
 namespace SPH
 {

@@ -367,6 +367,49 @@ static sphb200_status correctionMatrix(sphb200_relation *inner)
     return SPHB200_OK;
 }
 
+// registerStateVariableData<Matd>("DeformationGradient", IdentityMatrix<Matd>::value) (elastic_dynamics.cpp:60,70) and
+// registerStateVariableDataFrom<Vecd>("InitialPosition", "Position") (general_constraint.h:96): the initial value a variable
+// gets when it is FIRST registered - a caller that registered and filled it before keeps its values
+template <int D, class R>
+__global__ void __launch_bounds__(256) k_fill_identity(int64_t n, R *__restrict__ F)
+{
+    const int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n)
+        return;
+#pragma unroll
+    for (int a = 0; a < D; ++a)
+#pragma unroll
+        for (int c = 0; c < D; ++c)
+            F[i * D * D + a * D + c] = a == c ? R(1) : R(0);
+}
+template <int D, class R>
+static sphb200_status deformationGradientVar(sphb200_body *b, R **out)
+{
+    sphb200_ctx *ctx = b->ctx;
+    const bool fresh = b->find("DeformationGradient") == nullptr;
+    SPHB_TRY(getVarPtr<R>(b, "DeformationGradient", D * D, out, true));
+    if (fresh && b->n > 0)
+    {
+        k_fill_identity<D, R><<<gridFor(b->n, 256), 256, 0, ctx->stream>>>(b->n, *out);
+        SPHB_LAUNCH_CHECK(ctx);
+    }
+    return SPHB200_OK;
+}
+template <int D, class R>
+static sphb200_status initialPositionVar(sphb200_body *b, R **out)
+{
+    sphb200_ctx *ctx = b->ctx;
+    const bool fresh = b->find("InitialPosition") == nullptr;
+    SPHB_TRY(getVarPtr<R>(b, "InitialPosition", D, out, true));
+    if (fresh && b->n > 0)
+    {
+        R *pos;
+        SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos, true));
+        SPHB_CUDA(ctx, cudaMemcpyAsync(*out, pos, size_t(b->n) * D * sizeof(R), cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    return SPHB200_OK;
+}
+
 template <int D, class R>
 static sphb200_status solidFirstHalf(sphb200_relation *inner, int decomposed, double dt_)
 {
@@ -384,7 +427,7 @@ static sphb200_status solidFirstHalf(sphb200_relation *inner, int decomposed, do
     SPHB_TRY(getVarPtr<R>(b, "Mass", 1, &mass, true));
     SPHB_TRY(getVarPtr<R>(b, "Density", 1, &rho, true));
     SPHB_TRY(getVarPtr<R>(b, "LinearGradientCorrectionMatrix", D * D, &B));
-    SPHB_TRY(getVarPtr<R>(b, "DeformationGradient", D * D, &F, true));
+    SPHB_TRY((deformationGradientVar<D, R>(b, &F)));
     SPHB_TRY(getVarPtr<R>(b, "DeformationRate", D * D, &dF, true));
     SPHB_TRY(getVarPtr<R>(b, "DeterminantTerm", 1, &Jterm));
     SPHB_TRY(getVarPtr<R>(b, "StressOnParticle", D * D, &stress));
@@ -419,7 +462,7 @@ static sphb200_status solidSecondHalf(sphb200_relation *inner, double dt_)
     SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos, true));
     SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel, true));
     SPHB_TRY(getVarPtr<R>(b, "LinearGradientCorrectionMatrix", D * D, &B));
-    SPHB_TRY(getVarPtr<R>(b, "DeformationGradient", D * D, &F, true));
+    SPHB_TRY((deformationGradientVar<D, R>(b, &F)));
     SPHB_TRY(getVarPtr<R>(b, "DeformationRate", D * D, &dF, true));
     SPHB_TRY(ensureList(inner, 0));
     k_solid_second_half<D, R><<<gridFor(b->own_end - (b->own_begin & ~int64_t(31)), 128), 128, 0, ctx->stream>>>(
@@ -437,7 +480,7 @@ static sphb200_status solidConstrain(sphb200_body *b, const int64_t *ids, int64_
         return SPHB200_OK;
     R *pos, *pos0, *vel;
     SPHB_TRY(getVarPtr<R>(b, "Position", D, &pos, true));
-    SPHB_TRY(getVarPtr<R>(b, "InitialPosition", D, &pos0, true));
+    SPHB_TRY((initialPositionVar<D, R>(b, &pos0)));
     SPHB_TRY(getVarPtr<R>(b, "Velocity", D, &vel, true));
     SPHB_CUDA(ctx, ctx->scratch_a.ensure(size_t(m) * 8));
     SPHB_CUDA(ctx, cudaMemcpyAsync(ctx->scratch_a.p, ids, size_t(m) * 8, cudaMemcpyHostToDevice, ctx->stream));

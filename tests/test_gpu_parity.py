@@ -802,6 +802,87 @@ def test_reference_ck_main_on_the_cuda_policy_equals_the_python_harness(pk, gpu,
     assert abs(e[0] - 0.5) < 1e-12 and e[-1] < 0.25
 
 
+def _integration_exe(name):
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "integration", "_build", name)
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-s", "-C", os.path.join(root, "integration")])
+    if not os.path.exists(exe):
+        pytest.skip("integration binary was not built (needs the reference tree at build time)")
+    return exe
+
+
+@pytest.mark.gpu
+def test_reference_twisting_column_main_on_the_cuda_policy(pk, gpu, tmp_path):
+    """the reference's unmodified twisting_column.cpp on the CUDA policy: total-Lagrangian solid dynamics on the device,
+    the USER-DEFINED InitialCondition (a host local dynamics written in the main itself) through the generic host
+    fall-back of a device policy, FixBodyPartConstraint over a BodyRegionByParticle.  Its observer series equal the Python
+    harness's and - like them - the reference's stored run to its 6 printed digits"""
+    import json
+    import os
+    import subprocess
+    exe = _integration_exe("test_3d_twisting_column_cuda")
+    r = subprocess.run([exe, "--state_recording=0"], capture_output=True, text=True, cwd=tmp_path, timeout=900)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+    pos = np.loadtxt(tmp_path / "output" / "MyObserver_Position.dat", skiprows=1)
+    vel = np.loadtxt(tmp_path / "output" / "MyObserver_Velocity.dat", skiprows=1)
+    c = pk.cases.TwistingColumn(gpu, dp=0.1, real_bytes=8)
+    obs = [c.observed()]
+    while c.time < 0.5:
+        integ = 0.0
+        while integ < 0.5 / 250.0:
+            integ += c.step()
+            obs.append(c.observed())
+    assert pos.shape == (len(obs), 4) and vel.shape == (len(obs), 4) and len(obs) == 3127
+    # y and z of the axis point are zero by symmetry: rounding noise (1e-11) whose sign depends on libm's sin / atan2
+    assert np.allclose(pos[:, 1:], np.asarray([o[0] for o in obs]), rtol=1e-9, atol=1e-8)
+    assert np.allclose(vel[:, 1:], np.asarray([o[1] for o in obs]), rtol=1e-7, atol=1e-5)
+    gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "twisting_column_3d.json")))
+    ref = np.asarray(next(v["series"] for v in gold["quantities"]["MyObserver_Position"]["runs"].values() if v["stride"] == 1))[0]
+    assert np.abs(pos[:, 1:] - ref).max() < 2e-5 * np.abs(ref).max()       # the stored run, 6 printed digits
+
+
+@pytest.mark.gpu
+def test_reference_2d_dambreak_main_and_its_restart_on_the_cuda_policy(pk, gpu, tmp_path):
+    """the reference's unmodified 2-D Dambreak.cpp on the CUDA policy, to t = 20: energy and probe samples equal the Python
+    harness's; then row f2 from the C++ side - a second process started with --restart_step=2000 reads the state RestartIO
+    wrote through DiscreteVariable::synchronizeWithDevice, uploads it and continues: its samples from iteration 2200 on
+    equal the uninterrupted run's"""
+    import subprocess
+    exe = _integration_exe("test_2d_dambreak_cuda")
+    r = subprocess.run([exe, "--state_recording=0", "--regression=1"], capture_output=True, text=True, cwd=tmp_path, timeout=900)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+    energy = np.loadtxt(tmp_path / "output" / "WaterBody_TotalMechanicalEnergy.dat", skiprows=1)
+    probe = np.loadtxt(tmp_path / "output" / "FluidObserver_Pressure.dat", skiprows=1)
+    from oracle import validate_golden as vg
+    h = vg.dambreak_2d(23, backend=gpu)
+    n = len(h["ours_energy"])                  # 22 or 23: the run ends within a step of the last sampling iteration
+    assert energy.shape[0] == n >= 22 and probe.shape == (n, 2)
+    assert np.allclose(energy[:, 1], h["ours_energy"], rtol=1e-11, atol=0)
+    assert (tmp_path / "restart" / "Restart_2000.bin").exists()
+    first = {"energy": energy.copy(), "probe": probe.copy()}
+    r = subprocess.run([exe, "--state_recording=0", "--regression=1", "--restart_step=2000"], capture_output=True, text=True, cwd=tmp_path, timeout=900)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+    energy = np.loadtxt(tmp_path / "output" / "WaterBody_TotalMechanicalEnergy.dat", skiprows=1)
+    probe = np.loadtxt(tmp_path / "output" / "FluidObserver_Pressure.dat", skiprows=1)
+    # The restarted main records its first sample BEFORE its loop, from the reloaded state: the same state the uninterrupted
+    # run sampled at iteration 2000 (its 11th row) - time, energy and the probe's interpolated pressure must be the same
+    assert abs(energy[0, 0] - first["energy"][10, 0]) <= 1e-12 * energy[0, 0]
+    assert abs(energy[0, 1] - first["energy"][10, 1]) <= 1e-12 * energy[0, 1]
+    # the probe: the uninterrupted main samples with the PREVIOUS step's observer configuration (it updates the relations
+    # after sampling), the restarted one right after fluid_observer_contact.updateConfiguration() - the same field through
+    # neighbour weights one advection step apart
+    assert abs(probe[0, 1] - first["probe"][10, 1]) <= 0.02 * max(abs(probe[0, 1]), 1e-3)
+    # from there on the reference's restart convention repeats iteration 2000 (the counter resumes AT the restart step), so
+    # the samples are one advection step later than the uninterrupted run's: the same curve E(t), not the same rows
+    assert energy.shape[0] >= 12 and energy[-1, 0] > 19.0
+    interp = np.interp(energy[1:, 0], first["energy"][:, 0], first["energy"][:, 1])
+    inside = energy[1:, 0] <= first["energy"][-1, 0]
+    assert np.abs(energy[1:, 1][inside] - interp[inside]).max() < 5e-3
+
+
 @pytest.mark.gpu
 def test_run_level_observables_against_the_reference_fixtures(pk, gpu):
     """the CUDA path against the FULL stored series of the reference's own regression fixtures (tests/golden),
