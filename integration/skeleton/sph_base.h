@@ -155,6 +155,7 @@ class Shape
     bool isValid() const { return true; }
     virtual bool checkContain(const Vecd &p) = 0;
     virtual Vecd findClosestPoint(const Vecd &p) = 0;
+    virtual BoundingBoxd getBounds() { return BoundingBoxd(); } // base_geometry.h: bounding box of the shape
     // base_geometry.cpp:45-59: unit vector to the closest surface point, sign by containment
     Vecd findNormalDirection(const Vecd &p)
     {

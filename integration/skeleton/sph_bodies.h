@@ -273,6 +273,8 @@ class SPHSystem
     const BoundingBoxd &getSystemDomainBounds() const { return system_bounds_; }
     Real GlobalResolution() const { return global_resolution_; }
     bool GenerateRegressionData() const { return generate_regression_data_; }
+    void setReloadParticles(bool v) { reload_particles_ = v; }
+    bool ReloadParticles() const { return reload_particles_; }
     bool StateRecording() const { return state_recording_; }
     size_t RestartStep() const { return restart_step_; }
     template <typename DataType>
@@ -290,7 +292,7 @@ class SPHSystem
     BoundingBoxd system_bounds_;
     Real global_resolution_;
     SingleVariable<Real> physical_time_;
-    bool generate_regression_data_ = false, state_recording_ = true;
+    bool generate_regression_data_ = false, state_recording_ = true, reload_particles_ = false;
     size_t restart_step_ = 0;
     std::vector<RealBody *> real_bodies_;
     std::vector<SPHRelation *> relations_;
@@ -320,6 +322,11 @@ class SPHBody
     BaseParticles &getBaseParticles() { return *particles_; }
     BaseMaterial &getBaseMaterial() { return *material_; }
     BoundingBoxd getSPHSystemBounds() { return system_.getSystemDomainBounds(); }
+    BoundingBoxd getSPHBodyBounds() { return shape_->getBounds(); }
+    // addMaterialProperty<Viscosity>(mu) (base_body.h): the one property on the path is the dynamic viscosity
+    template <class PropertyType, typename... Args>
+    void addMaterialProperty(Args &&...args) { viscosity_ = Real(PropertyType(std::forward<Args>(args)...).ReferenceViscosity()); }
+    Real ReferenceViscosity() const { return viscosity_; }
     template <class AdaptationType, typename... Args>
     void defineAdaptation(Args &&...args)
     {
@@ -363,6 +370,13 @@ class SPHBody
     }
     template <class ParticleType>
     void generateParticles(const StdVec<Vecd> &positions) { createParticles(positions, Real(0)); }
+    // generateParticles<BaseParticles, Reload>(name): relaxed positions from a reload file - out of scope here
+    template <class ParticleType, class Method>
+    void generateParticles(const std::string &)
+    {
+        std::cout << "\n Error: particle reload files are not supported by the integration skeleton." << std::endl;
+        std::exit(1);
+    }
     void *device_body_ = nullptr; // owned by the device back end
     bool device_cell_list_ready_ = false;
 
@@ -381,6 +395,7 @@ class SPHBody
     std::unique_ptr<SPHAdaptation> adaptation_;
     std::unique_ptr<BaseMaterial> material_;
     std::unique_ptr<BaseParticles> particles_;
+    Real viscosity_ = Real(0);
 };
 
 class RealBody : public SPHBody

@@ -19,11 +19,13 @@ class ParallelCudaPolicy;
 #include "sph_io.h"
 #include "sph_ck.h"
 #include "sph_solid.h"
+#include "sph_periodic.h"
 #ifdef SPHINXSYS_USE_CUDA
 #include "sph_cuda.h"
 #include "sph_cuda_dynamics.h"
 #include "sph_cuda_ck.h"
 #include "sph_cuda_solid.h"
+#include "sph_cuda_periodic.h"
 #else
 namespace SPH
 {

@@ -77,7 +77,8 @@ inline sphb200_body *bodyHandle(SPHBody &body)
             check(sphb200_body_set_elastic(h, double(e->ReferenceDensity()), double(e->YoungsModulus()), double(e->PoissonRatio())), ctx,
                   "defineMatterMaterial");
         else if (auto *f = dynamic_cast<Fluid *>(&body.getBaseMaterial()))
-            check(sphb200_body_set_fluid(h, double(f->ReferenceDensity()), double(f->ReferenceSoundSpeed()), 0.0), ctx, "defineMatterMaterial");
+            check(sphb200_body_set_fluid(h, double(f->ReferenceDensity()), double(f->ReferenceSoundSpeed()), double(body.ReferenceViscosity())), ctx,
+                  "defineMatterMaterial");
         else
             check(sphb200_body_set_fluid(h, double(body.getBaseMaterial().ReferenceDensity()), 1.0, 0.0), ctx, "defineMatterMaterial");
     }
