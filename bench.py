@@ -409,8 +409,13 @@ def single_gpu(a, pk, stream, device, warmup, R, with_cpu, short=False):
             # host arrays define the particle order: rebuild cell list + configuration as the
             # reference does after a reload (Dambreak.cpp:132-138)
             w.update_cell_list()
-            case.update_configuration()
-            case.advection_step()
+            case.update_configuration(observer=False)
+            # the step without its closing re-configuration of the fluid relations: the next step's state comes from the
+            # host again and is configured then; the probes are interpolated on the moved particles, which needs the
+            # cell list of the new positions and the observer's contact relation only
+            case.advection_step(reconfigure=False)
+            w.update_cell_list()
+            case.obs_contact.update()
             # the step's result: the observables the reference's regression tests record (energy, probe pressures)
             return case.mechanical_energy(), case.probe_pressure()
 
@@ -435,8 +440,10 @@ def single_gpu(a, pk, stream, device, warmup, R, with_cpu, short=False):
                "note": "every timed step uploads the whole evolving fluid state (10 variables) from pinned host arrays "
                        "(sphb200_var_stage + sphb200_body_commit_staged: double-buffered, the copy of step k+1's inputs runs on a "
                        "copy stream while step k computes; all copies lie inside the timed region, whose end waits for the device), "
-                       "rebuilds cell list + relations, runs one advection step and reads back the step's results: total "
-                       "mechanical energy, the 6 probe pressures and the dt values.  The host arrays hold the state captured "
+                       "rebuilds cell list + relations, runs one advection step (Dt, density summation, the acoustic sub-steps), "
+                       "re-bins the moved particles for the observer's contact relation and reads back the step's results: total "
+                       "mechanical energy, the 6 probe pressures and the dt values.  The fluid relations are NOT rebuilt a second "
+                       "time at the end of the step: the next step's state comes from the host and is configured then.  The host arrays hold the state captured "
                        "after the resident leg and are not refreshed, so every timed step integrates the same state; updated "
                        "particle state crosses back only at output intervals (output_interval_leg), as in the reference"}
 

@@ -184,8 +184,10 @@ class DamBreak:
         S.integration_2nd_half(self.inner, self.wall_contact, True, dt)
         self.n_acoustic += 1
 
-    def advection_step(self, sort_interval=100, observer=True, before_configuration=None):
+    def advection_step(self, sort_interval=100, observer=True, before_configuration=None, reconfigure=True):
         """one outer iteration of dambreak.cpp:159-195; returns (Dt, number of acoustic sub-steps).
+        reconfigure=False leaves out the closing cell-list / relation update (a caller that replaces the state from the
+        host before the next step rebuilds the configuration then anyway).
         before_configuration(): called between the sub-step loop and the configuration update, where
         the 2-D main samples its observables (Dambreak.cpp:196-207, i.e. with the previous step's
         observer configuration)"""
@@ -214,6 +216,8 @@ class DamBreak:
         if before_configuration is not None:
             before_configuration()
         self.n_advection += 1
+        if not reconfigure:
+            return Dt, k
         if sort_interval and self.n_advection % sort_interval == 0 and self.n_advection != 1:
             w.sort()
         w.update_cell_list()

@@ -156,6 +156,23 @@ def test_ck_flavour_dynamics(pk, gpu, oracle, ndim, dp, real_bytes):
     assert out["gpu"]["Compression"].min() >= 1.0 and out["gpu"]["DensityInternal"].min() < 1.0
 
 
+def test_step_without_closing_reconfiguration_gives_the_same_observables(pk, gpu):
+    """bench.py's e2e leg: advection_step(reconfigure=False) + cell list + observer relation only - energy and probe
+    pressures bit-identical to the full step (whose closing update of the fluid relations the next reload would redo)"""
+    probes = [[x, 0.2, 0.25] for x in (0.4, 1.1, 1.9)]
+    a = pk.cases.DamBreak(gpu, ndim=3, dp=0.05, real_bytes=8, probes=probes)
+    b = pk.cases.DamBreak(gpu, ndim=3, dp=0.05, real_bytes=8, probes=probes)
+    for _ in range(3):
+        a.advection_step()
+        b.advection_step()
+    ra = a.advection_step()
+    rb = b.advection_step(reconfigure=False)
+    b.water.update_cell_list()
+    b.obs_contact.update()
+    assert ra == rb and a.mechanical_energy() == b.mechanical_energy()
+    assert np.array_equal(a.probe_pressure(), b.probe_pressure()) and np.abs(a.probe_pressure()).max() > 1e-3
+
+
 CK_FIELDS = ("Position", "Velocity", "Density", "Pressure", "Compression", "CompressionRate", "Force", "Displacement",
              "VolumetricMeasure", "LinearCorrectionMatrix")
 
