@@ -592,6 +592,24 @@ class SlabDamBreak:
             P.case.update_configuration(observer=P.case.observer is not None)
         self._halo_maps()
 
+    def close(self):
+        """release the peer mappings and landing buffers (every rank: the mappings first, then - after a barrier - the
+        allocations they point into) and the slabs' contexts"""
+        if self.peer_halo:
+            torch.cuda.synchronize()
+            inside_one_process = isinstance(self.comm, LocalComm)
+            for P in self.parts:
+                for ptr in (P.peer_left, P.peer_right):
+                    if ptr is not None and not inside_one_process:
+                        P.case.sys.peer_close(ptr)
+            self.comm.barrier()
+            for P in self.parts:
+                P.case.sys.peer_free(P.peer_base)
+            self.peer_halo = False
+        for P in self.parts:
+            P.case.sys.close()
+        self.parts = []
+
     # ---- observables / inspection -------------------------------------------------------------------
     def n_fluid(self):
         return int(self.comm.allreduce([float(sum(P.oe - P.ob for P in self.parts))], "sum"))

@@ -62,5 +62,6 @@ if one is not None:
     assert nf == one.water.n and abs(e1 - en) <= 1e-12 * abs(e1), (nf, e1, en)
     print(f"slab nccl parity ok: world={comm.world} dp={dp} steps={steps} n_fluid={nf} sub-steps={many.n_acoustic} "
           f"max rel-L2 {max(worst.values()):.2e} energy {en!r} cuts={many.cuts}", flush=True)
+many.close()            # IPC mappings closed before the owners free their landing buffers
 dist.barrier()
 dist.destroy_process_group()
