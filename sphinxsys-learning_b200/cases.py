@@ -200,7 +200,7 @@ class DamBreak:
             k, self.dt, _, relaxation = S.acoustic_relaxation(self.inner, self.wall_contact, True, True, Dt, 0.6,
                                                               order=1 if self.ndim == 3 else 0, dt_carry=self.dt,
                                                               max_substeps=self._substeps_guess)
-            self._substeps_guess = k + 1
+            self._substeps_guess = max(k, 1)   # steady state: exactly the launches that are needed, none that returns at once
             self.time += relaxation
             self.n_acoustic += k
         while relaxation < Dt:
@@ -359,7 +359,7 @@ class TaylorGreen:
         if self.fused_loop and hasattr(S, "acoustic_relaxation"):
             k, _, _, relaxation = S.acoustic_relaxation(self.inner, None, True, False, Dt, 0.6, order=2,
                                                         max_substeps=self._substeps_guess)
-            self._substeps_guess = k + 1
+            self._substeps_guess = max(k, 1)   # steady state: exactly the launches that are needed, none that returns at once
             self.time += relaxation
         while relaxation < Dt:
             dt = min(S.acoustic_dt(w), Dt)
