@@ -213,7 +213,8 @@ def slab_main(a, pk, stream, rank, world, local_rank, warmup):
             # this step's state was copied host -> device on the copy stream while the previous step computed; the host
             # rows (owned + halo of the captured arrangement) define the slab again, as a reload does: n back to the
             # captured count, commit (ids restart), the next upload starts, then cell list (owned pages) + relations +
-            # halo maps and one full advection step (which ends with migration + re-decomposition)
+            # halo maps and one advection step without its closing migration / re-decomposition (the next step's slab comes
+            # from the host again and is configured then)
             w.resize(n0)
             stage_pending[0] or stage_inputs()
             w.commit_staged()
@@ -222,7 +223,7 @@ def slab_main(a, pk, stream, rank, world, local_rank, warmup):
             w.update_cell_list()
             P.case.update_configuration(observer=False)
             case._halo_maps()
-            case.advection_step()
+            case.advection_step(reconfigure=False)
             case.mechanical_energy()
 
         stage_pending = [False]
@@ -234,7 +235,8 @@ def slab_main(a, pk, stream, rank, world, local_rank, warmup):
                "note": "per rank: the slab's whole evolving fluid state (owned + halo rows, 11 variables) is uploaded from pinned host "
                        "arrays every step, double-buffered (sphb200_var_stage on a copy stream while the previous step computes, "
                        "sphb200_body_commit_staged with reload semantics), then cell list + relations + halo maps are rebuilt and one "
-                       "advection step runs (ending with migration and re-decomposition); read back: the all-reduced total mechanical "
+                       "advection step runs (Dt, density summation, the acoustic sub-steps with their halo refreshes; not the closing migration, "
+                       "which the next reload replaces); read back: the all-reduced total mechanical "
                        "energy and the loop state; the host arrays hold the captured state and are not refreshed; bytes are rank 0's x N"}
 
     if rank == 0:

@@ -464,7 +464,9 @@ class SlabDamBreak:
         for P in self.parts:
             P.case.sys.substep_ctl(P.case.water, 0.6, 1, 1)
 
-    def advection_step(self):
+    def advection_step(self, reconfigure=True):
+        """reconfigure=False leaves out the closing migration / re-decomposition (a caller that reloads the slabs from the
+        host before the next step configures them then anyway)"""
         Dt = self._min_over_slabs(lambda P: P.case.sys.advection_dt(P.case.water, self.U_ref))
         for P in self.parts:
             P.case.sys.density_summation(P.case.inner, P.case.wall_contact, free_surface=True)
@@ -493,7 +495,8 @@ class SlabDamBreak:
             self.time += self.dt
             k += 1
         self.n_advection += 1
-        self.reconfigure()
+        if reconfigure:
+            self.reconfigure()
         return Dt, k
 
     def fluid_per_page(self):
