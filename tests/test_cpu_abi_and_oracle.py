@@ -234,3 +234,24 @@ def test_ck_acoustic_oracle_agrees_with_an_independent_restatement(pk, oracle):
         err = np.linalg.norm(got - ref) / max(np.linalg.norm(ref), 1e-300)
         assert err < 1e-10, (name, err)
     assert abs(o.mechanical_energy() - m.energy()) < 1e-12
+
+
+@pytest.mark.parametrize("ndim,dp,weight,side", [(2, 0.025, 2.0, 0.5), (3, 0.05, 1.0, 0.25)])
+def test_force_on_structure_oracle_hydrostatic_known_answer(pk, oracle, ndim, dp, weight, side):
+    """row f4, a physical known-answer for the restatement of FSI::PressureForceFromFluid (no reference fixture pins it):
+    the water column at rest with hydrostatic pressure rho g (H - y) pushes the tank down with its weight rho g V and the
+    wall it leans on sideways with rho g H^2 / 2 (x width); nothing along z; no viscous force without motion.  The SPH sum
+    reaches both within the kernel-truncation error of the boundary (4-7 % at these resolutions), with the right signs."""
+    c = pk.cases.DamBreakCK(oracle, ndim=ndim, dp=dp, real_bytes=8, with_observer=False)
+    w, s, S = c.water, c.wall, c.sys
+    w.set("Pressure", (1.0 - w.get("Position")[:, 1]).astype(np.float64))
+    rel = S.contact(s, [w])
+    rel.update()
+    S.ck_pressure_force_from_fluid(rel, False)
+    total = s.get("PressureForceFromFluid").sum(0)
+    assert abs(total[1] + weight) < 0.08 * weight and abs(total[0] + side) < 0.08 * side, total
+    if ndim == 3:
+        assert abs(total[2]) < 1e-12
+    assert np.allclose(s.get("ForcePrior"), s.get("PressureForceFromFluid"))       # ForcePriorCK: prior started at zero
+    S.ck_viscous_force_from_fluid(rel, False)
+    assert np.abs(s.get("ViscousForceFromFluid")).max() == 0.0
