@@ -255,3 +255,19 @@ def test_force_on_structure_oracle_hydrostatic_known_answer(pk, oracle, ndim, dp
     assert np.allclose(s.get("ForcePrior"), s.get("PressureForceFromFluid"))       # ForcePriorCK: prior started at zero
     S.ck_viscous_force_from_fluid(rel, False)
     assert np.abs(s.get("ViscousForceFromFluid")).max() == 0.0
+
+
+def test_ck_correction_matrix_oracle_lattice_known_answer(pk, oracle):
+    """LinearCorrectionMatrix on the undisturbed lattice: in the interior the moment matrix -sum r_ij (x) grad W_ij V_j is
+    isotropic and within the kernel's discretisation error of the identity (h = 1.3 dp: 0.979), so its inverse is
+    1.0214 I - off-diagonals at rounding level, the same on every interior particle"""
+    c = pk.cases.DamBreakCK(oracle, ndim=3, dp=0.05, real_bytes=8, with_observer=False)
+    c.sys.ck_linear_correction_matrix(c.inner, c.wall_contact, 0.0)
+    B = c.water.get("LinearCorrectionMatrix").reshape(-1, 3, 3)
+    pos = c.water.get("Position")
+    interior = np.all((pos > 0.2) & (pos < np.array([1.8, 0.8, 0.3])), axis=1)
+    assert interior.sum() > 500
+    diag = B[interior][:, [0, 1, 2], [0, 1, 2]]
+    assert np.abs(diag - diag[0, 0]).max() < 1e-12 and abs(diag[0, 0] - 1.0) < 0.03
+    off = B[interior] - diag[:, :, None] * np.eye(3)
+    assert np.abs(off).max() < 1e-12
