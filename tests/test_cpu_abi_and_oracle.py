@@ -44,7 +44,7 @@ def test_cpp_adapter_main_builds_and_fails_loudly_without_a_gpu(pk):
     assert r.returncode == 1 and "no CUDA device" in r.stderr
 
 
-def test_reference_main_compiles_unmodified_on_the_cuda_policy():
+def test_reference_main_compiles_unmodified_on_the_cuda_policy(tmp_path):
     """integration/: the reference's tests/3d_examples/test_3d_dambreak/dambreak.cpp and the CK main
     tests/tests_sycl/3d_examples/test_3d_dambreak_sycl/dambreak.cpp, read where they lie and not a byte changed, compile against the class skeleton + the CUDA execution policy (src_cuda) + libsphb200; without a GPU the
     binary fails loudly (the reference's convention: message + exit 1)"""
@@ -66,7 +66,7 @@ def test_reference_main_compiles_unmodified_on_the_cuda_policy():
         assert os.path.exists(exe), name
         if torch.cuda.is_available():
             continue  # a GPU is present: the run itself is covered by the gpu tests
-        r = subprocess.run([exe, "--state_recording=0"], capture_output=True, text=True)
+        r = subprocess.run([exe, "--state_recording=0"], capture_output=True, text=True, cwd=tmp_path)
         assert r.returncode == 1 and "no CUDA device" in r.stdout + r.stderr, name
 
 
