@@ -26,7 +26,9 @@ class ParallelCudaPolicy;
 #include "sph_cuda_ck.h"
 #include "sph_cuda_solid.h"
 #include "sph_cuda_periodic.h"
+#include "sph_cuda_solver.h"
 #else
+#include "sph_solver.h"
 namespace SPH
 {
 inline void attachExecutionBackEnd(SPHBody &) {}

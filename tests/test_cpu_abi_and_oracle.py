@@ -58,8 +58,9 @@ def test_reference_main_compiles_unmodified_on_the_cuda_policy(tmp_path):
     assert "$(REF)/tests/2d_examples/test_2d_dambreak/Dambreak.cpp" in mk
     assert "$(REF)/tests/3d_examples/test_3d_twisting_column/twisting_column.cpp" in mk
     assert "$(REF)/tests/2d_examples/test_2d_taylor_green/taylor_green.cpp" in mk
+    assert "$(REF)/tests/tests_sycl/2d_examples/test_2d_dambreak_sycl/dambreak_sycl.cpp" in mk
     for name in ("test_3d_dambreak_cuda", "test_3d_dambreak_ck_cuda", "test_2d_dambreak_cuda", "test_3d_twisting_column_cuda",
-                 "test_2d_taylor_green_cuda"):
+                 "test_2d_taylor_green_cuda", "test_2d_dambreak_ck_cuda"):
         exe = os.path.join(ROOT, "integration", "_build", name)
         if not os.path.exists("/root/reference") and not os.path.exists(exe):
             pytest.skip("reference tree absent and no prebuilt binary")

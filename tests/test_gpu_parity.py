@@ -885,6 +885,26 @@ def test_reference_taylor_green_main_on_the_cuda_policy(pk, gpu, tmp_path):
 
 
 @pytest.mark.gpu
+def test_reference_2d_ck_main_with_the_solver_api_on_the_cuda_policy(pk, gpu, tmp_path):
+    """the reference's unmodified tests_sycl/2d_examples/test_2d_dambreak_sycl/dambreak_sycl.cpp: the solver form of the CK API
+    (SPHSolver, ParticleMethodContainer factories with chained post-contact / post-state dynamics, TimeStepper with its
+    interval triggers - one loop of acoustic steps, advection-step work when the trigger fires).  Its 23 energy and probe
+    samples equal the Python harness's (cases.DamBreakCK.acoustic_step_2d)"""
+    import subprocess
+    exe = _integration_exe("test_2d_dambreak_ck_cuda")
+    r = subprocess.run([exe, "--state_recording=0"], capture_output=True, text=True, cwd=tmp_path, timeout=900)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+    energy = np.loadtxt(tmp_path / "output" / "WaterBody_TotalMechanicalEnergy.dat", skiprows=1)
+    probe = np.loadtxt(tmp_path / "output" / "FluidObserver_Pressure.dat", skiprows=1)
+    from oracle import validate_golden as vg
+    h = vg.dambreak_2d_ck(23, backend=gpu)
+    n = len(h["ours_energy"])                  # the harness stops at the fixture's 23 samples, the main runs on to t = 20
+    assert n == 23 and energy.shape[0] >= n and probe.shape == energy.shape
+    assert np.allclose(energy[:n, 1], h["ours_energy"], rtol=1e-10, atol=0)
+    assert (tmp_path / "restart" / "Restart_2000.bin").exists()          # RestartIOCK wrote through the device delegation
+
+
+@pytest.mark.gpu
 def test_reference_2d_dambreak_main_and_its_restart_on_the_cuda_policy(pk, gpu, tmp_path):
     """the reference's unmodified 2-D Dambreak.cpp on the CUDA policy, to t = 20: energy and probe samples equal the Python
     harness's; then row f2 from the C++ side - a second process started with --restart_step=2000 reads the state RestartIO
